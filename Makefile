@@ -1,0 +1,98 @@
+# Build of the native parts (replaces /root/reference/Makefile:19-51, which had no optimisation
+# flag, no -arch, and no rule for the MPI+GPU program).
+#
+#   make cpu        libb200cnn_cpu.so + bin/cnn bin/cnnmpi bin/mkidx
+#   make cuda       libb200cnn_cuda.so (sm_100a kernels, engine, comm) + bin/cudacnn
+#   make all        both
+#   make sass       SASS / resource listings of every kernel under profiles/sass/
+#   make test_serial / test_mpi / test_cuda    the reference's run targets on synthetic data
+#
+# Shared objects are built IN TREE under mpi_cuda_cnn_b200/lib so they travel with the source
+# snapshot to the GPU box; they are git-ignored.
+
+CXX      ?= g++
+NVCC     ?= /usr/local/cuda/bin/nvcc
+# -ffp-contract=off: the quirks mode of the CPU engine promises bit-identical results with the
+# reference binary, which is built without FMA contraction.
+CXXFLAGS ?= -O3 -std=c++17 -fPIC -Wall -Wextra -ffp-contract=off
+NVARCH   ?= -gencode arch=compute_100a,code=sm_100a
+NVFLAGS  ?= -O3 -std=c++17 $(NVARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall --expt-relaxed-constexpr
+
+PKG    := mpi_cuda_cnn_b200
+LIBDIR := $(PKG)/lib
+BINDIR := bin
+OBJDIR := build
+
+CPU_SRCS := csrc/cpu/idx.cpp csrc/cpu/net.cpp csrc/cpu/comm.cpp csrc/cpu/trainer.cpp csrc/cpu/capi.cpp
+CPU_OBJS := $(patsubst csrc/cpu/%.cpp,$(OBJDIR)/cpu/%.o,$(CPU_SRCS))
+
+CUDA_SRCS := $(wildcard csrc/cuda/*.cu) $(wildcard csrc/comm/*.cu)
+CUDA_OBJS := $(patsubst csrc/%.cu,$(OBJDIR)/%.o,$(CUDA_SRCS))
+CUDA_HDRS := $(wildcard csrc/cuda/*.cuh) $(wildcard csrc/comm/*.cuh) $(wildcard include/*.h)
+
+.PHONY: all cpu cuda clean sass test_serial test_mpi test_cuda get_mnist
+
+all: cpu cuda
+
+cpu: $(LIBDIR)/libb200cnn_cpu.so $(BINDIR)/cnn $(BINDIR)/cnnmpi $(BINDIR)/mkidx
+
+cuda: $(LIBDIR)/libb200cnn_cuda.so $(BINDIR)/cudacnn
+
+$(OBJDIR)/cpu/%.o: csrc/cpu/%.cpp $(wildcard csrc/cpu/*.hpp) include/b200cnn_cpu.h
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+
+$(LIBDIR)/libb200cnn_cpu.so: $(CPU_OBJS)
+	@mkdir -p $(LIBDIR)
+	$(CXX) -shared -o $@ $^ -lrt -lm
+
+$(BINDIR)/cnn: csrc/cpu/cnn_main.cpp $(CPU_OBJS)
+	@mkdir -p $(BINDIR)
+	$(CXX) $(CXXFLAGS) -o $@ $^ -lrt -lm
+
+$(BINDIR)/cnnmpi: csrc/cpu/cnnmpi_main.cpp $(CPU_OBJS)
+	@mkdir -p $(BINDIR)
+	$(CXX) $(CXXFLAGS) -o $@ $^ -lrt -lm
+
+$(BINDIR)/mkidx: csrc/cpu/mkidx_main.cpp $(OBJDIR)/cpu/idx.o
+	@mkdir -p $(BINDIR)
+	$(CXX) $(CXXFLAGS) -o $@ $^
+
+$(OBJDIR)/%.o: csrc/%.cu $(CUDA_HDRS)
+	@mkdir -p $(dir $@)
+	$(NVCC) $(NVFLAGS) -Xptxas -v -Iinclude -Icsrc -c $< -o $@ 2> $(@:.o=.ptxas.log) || (cat $(@:.o=.ptxas.log); false)
+
+$(LIBDIR)/libb200cnn_cuda.so: $(CUDA_OBJS)
+	@mkdir -p $(LIBDIR)
+	$(NVCC) $(NVARCH) -shared -o $@ $^ -lcudart
+
+$(BINDIR)/cudacnn: csrc/apps/cudacnn_main.cpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o
+	@mkdir -p $(BINDIR)
+	$(CXX) $(CXXFLAGS) -Iinclude -I/usr/local/cuda/include -o $@ csrc/apps/cudacnn_main.cpp $(OBJDIR)/cpu/idx.o \
+	    -L$(LIBDIR) -lb200cnn_cuda -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$$ORIGIN/../$(LIBDIR)'
+
+sass: $(LIBDIR)/libb200cnn_cuda.so
+	@mkdir -p profiles/sass
+	cuobjdump -sass $< > profiles/sass/libb200cnn_cuda.sass
+	cuobjdump -res-usage $< > profiles/sass/libb200cnn_cuda.resources.txt 2>&1 || true
+	python tools/sass_summary.py profiles/sass/libb200cnn_cuda.sass > profiles/sass/SUMMARY.md
+
+DATADIR ?= build/data
+get_mnist: $(BINDIR)/mkidx
+	@mkdir -p $(DATADIR)
+	$(BINDIR)/mkidx $(DATADIR) 2000 400
+
+MNIST_ARGS = $(DATADIR)/train-images-idx3-ubyte $(DATADIR)/train-labels-idx1-ubyte \
+             $(DATADIR)/t10k-images-idx3-ubyte $(DATADIR)/t10k-labels-idx1-ubyte
+
+test_serial: $(BINDIR)/cnn get_mnist
+	$(BINDIR)/cnn --nepoch 1 --timing $(MNIST_ARGS)
+
+test_mpi: $(BINDIR)/cnnmpi get_mnist
+	$(BINDIR)/cnnmpi -np 2 --nepoch 1 --timing $(MNIST_ARGS)
+
+test_cuda: $(BINDIR)/cudacnn get_mnist
+	$(BINDIR)/cudacnn --nepoch 1 --batch-size 256 --timing $(MNIST_ARGS)
+
+clean:
+	rm -rf $(OBJDIR) $(BINDIR) $(LIBDIR)/*.so
