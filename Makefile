@@ -11,12 +11,12 @@
 # snapshot to the GPU box; they are git-ignored.
 
 CXX      ?= g++
-NVCC     ?= /usr/local/cuda/bin/nvcc
+NVCC     := /usr/local/cuda/bin/nvcc
 # -ffp-contract=off: the quirks mode of the CPU engine promises bit-identical results with the
 # reference binary, which is built without FMA contraction.
 CXXFLAGS ?= -O3 -std=c++17 -fPIC -Wall -Wextra -ffp-contract=off
-NVARCH   ?= -gencode arch=compute_100a,code=sm_100a
-NVFLAGS  ?= -O3 -std=c++17 $(NVARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall --expt-relaxed-constexpr
+SM_ARCH  := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS  := -O3 -std=c++17 $(SM_ARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall --expt-relaxed-constexpr
 
 PKG    := mpi_cuda_cnn_b200
 LIBDIR := $(PKG)/lib
@@ -64,7 +64,7 @@ $(OBJDIR)/%.o: csrc/%.cu $(CUDA_HDRS)
 
 $(LIBDIR)/libb200cnn_cuda.so: $(CUDA_OBJS)
 	@mkdir -p $(LIBDIR)
-	$(NVCC) $(NVARCH) -shared -o $@ $^ -lcudart
+	$(NVCC) $(SM_ARCH) -shared -o $@ $^ -lcudart
 
 $(BINDIR)/cudacnn: csrc/apps/cudacnn_main.cpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o
 	@mkdir -p $(BINDIR)

@@ -1,0 +1,429 @@
+// Fused gradient all-reduce + 1/world scaling + SGD update over NVLink 5 / NVSwitch (K8), the weight
+// broadcast (K9) and a device-side barrier.  See include/b200cnn_comm.h for the contract and the
+// reference code this replaces (/root/reference/cnnmpi.c:487-499 + cnn.c:303-311).
+//
+// Three variants of the same operation:
+//   one-shot  every rank loads the slice from all W ranks (its own included) in rank order, adds,
+//             updates its own weights.  (W-1)*N bytes in per GPU, one flag exchange.  Small slices.
+//   two-shot  rank r owns 1/W of the slice: loads that shard from all ranks, adds, computes the
+//             UPDATED WEIGHTS and stores them into every rank's parameter buffer.  2*(W-1)/W*N bytes
+//             per direction per GPU, two flag exchanges.  Replicas are identical by construction.
+//   NVLS      two-shot where the switch does the adding and the fan-out:
+//             multimem.ld_reduce.add.v4.f32 on the multicast address, multimem.st of the new weights.
+//
+// Ordering: flag words carry a per-block sequence number that only ever grows; a rank publishes with
+// st.release.sys after a CTA barrier and waits with ld.acquire.sys.  Waits give up after ~2 s and
+// raise an error flag rather than hanging the GPU.
+#include <new>
+
+#include "../cuda/common.cuh"
+#include "b200cnn_comm.h"
+#include "comm.cuh"
+
+namespace b200cnn {
+
+constexpr int kMaxRanks = B200CNN_COMM_MAX_RANKS;
+constexpr int kMaxBlocks = 128;
+constexpr int kCommThreads = 512;
+constexpr long long kSpinTimeoutCycles = 4000000000ll;  // ~2 s at 1.9 GHz
+
+static_assert(kMaxBlocks * 2 * kMaxRanks * sizeof(uint32_t) <= B200CNN_COMM_FLAG_BYTES, "flag block too small");
+
+struct CommView {
+    int rank, world, emulate;
+    char* region[kMaxRanks];
+    char* mc_region;
+    size_t params_off, grads_off[2];
+    uint32_t* seq;     // local sequence counters [emulate ? world : 1][kMaxBlocks]
+    uint32_t* errflag; // local
+};
+
+enum Op { kOpSgd = 0, kOpReduceOnly = 1, kOpBroadcast = 2, kOpBarrier = 3 };
+
+namespace {
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Peer data: coherent at system scope, never served from a stale L1 line.
+__device__ __forceinline__ float4 ld_peer(const float4* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_peer(float4* p, const float4& v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float4* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(mc)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st(float4* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+                 "f"(v.w)
+                 : "memory");
+}
+
+__device__ __forceinline__ uint32_t* flag_ptr(char* region, int block, int phase, int src) {
+    return reinterpret_cast<uint32_t*>(region) + (block * 2 + phase) * kMaxRanks + src;
+}
+
+// Cross-rank barrier between the blocks with this blockIdx.x on every rank.  All earlier global
+// writes of the CTA are published (CTA barrier, then a cumulative release at system scope).
+__device__ void signal_and_wait(const CommView& v, int rank, int phase, uint32_t seq) {
+    __syncthreads();
+    if (threadIdx.x < v.world && int(threadIdx.x) != rank) {
+        const int peer = threadIdx.x;
+        st_release_sys(flag_ptr(v.region[peer], blockIdx.x, phase, rank), seq);
+        const uint32_t* mine = flag_ptr(v.region[rank], blockIdx.x, phase, peer);
+        const long long t0 = clock64();
+        while (int32_t(ld_acquire_sys(mine) - seq) < 0) {
+            if (clock64() - t0 > kSpinTimeoutCycles) {
+                atomicExch(v.errflag, 1u);
+                break;
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 add4(float4 a, const float4& b) {
+    a.x += b.x;
+    a.y += b.y;
+    a.z += b.z;
+    a.w += b.w;
+    return a;
+}
+
+// Sum of element i over ranks 0..W-1 in that fixed order (identical on every rank).
+template <int W>
+__device__ __forceinline__ float4 reduce_ranks(const float4* const* g, int world, size_t i) {
+    float4 vals[W > 0 ? W : 1];
+    if (W > 0) {
+#pragma unroll
+        for (int k = 0; k < W; k++) vals[k] = ld_peer(g[k] + i);  // all loads in flight before the adds
+        float4 acc = vals[0];
+#pragma unroll
+        for (int k = 1; k < W; k++) acc = add4(acc, vals[k]);
+        return acc;
+    } else {
+        float4 acc = ld_peer(g[0] + i);
+        for (int k = 1; k < world; k++) acc = add4(acc, ld_peer(g[k] + i));
+        return acc;
+    }
+}
+
+template <int W>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ lr_dev, float lr_imm, int algo,
+                 int parity, int op, int root) {
+    const int rank = v.emulate ? int(blockIdx.y) : v.rank;
+    const int world = v.world;
+    uint32_t* seq_slot = v.seq + (v.emulate ? rank : 0) * kMaxBlocks + blockIdx.x;
+    const uint32_t seq = *seq_slot + 1;
+
+    signal_and_wait(v, rank, 0, seq);  // every rank's inputs for this call are complete
+
+    const float4* g[kMaxRanks];
+#pragma unroll
+    for (int k = 0; k < kMaxRanks; k++)
+        g[k] = reinterpret_cast<const float4*>(v.region[k < world ? k : 0] + v.grads_off[parity]) + off4;
+    float4* w_local = reinterpret_cast<float4*>(v.region[rank] + v.params_off) + off4;
+    float4* g_local = reinterpret_cast<float4*>(v.region[rank] + v.grads_off[parity]) + off4;
+    const float lr = (lr_dev ? *lr_dev : lr_imm) / float(world);
+    const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x, nthreads = size_t(gridDim.x) * blockDim.x;
+
+    bool need_exit_barrier = false;
+    if (op == kOpBarrier) {
+        // nothing to move
+    } else if (op == kOpBroadcast) {
+        const float4* src = reinterpret_cast<const float4*>(v.region[root] + v.params_off) + off4;
+        if (rank != root)
+            for (size_t i = tid; i < n4; i += nthreads) w_local[i] = ld_peer(src + i);
+        need_exit_barrier = true;  // root must not change its parameters before everyone has read them
+    } else if (algo == B200CNN_ALGO_ONE_SHOT) {
+        if (op == kOpSgd) {
+            for (size_t i = tid; i < n4; i += nthreads) {
+                const float4 s = reduce_ranks<W>(g, world, i);
+                float4 w = w_local[i];
+                w.x -= lr * s.x;
+                w.y -= lr * s.y;
+                w.z -= lr * s.z;
+                w.w -= lr * s.w;
+                w_local[i] = w;
+            }
+        } else {
+            // In-place all-reduce: peers are still reading this rank's slice, so results may only
+            // be written after everyone has finished reading.
+            // (Each thread keeps its results in registers across the barrier when they fit; otherwise
+            //  this falls back to two-shot, which the host selects for large slices anyway.)
+            float4 keep[4];
+            int nkeep = 0;
+            for (size_t i = tid; i < n4 && nkeep < 4; i += nthreads) keep[nkeep++] = reduce_ranks<W>(g, world, i);
+            signal_and_wait(v, rank, 1, seq);
+            nkeep = 0;
+            for (size_t i = tid; i < n4 && nkeep < 4; i += nthreads) g_local[i] = keep[nkeep++];
+        }
+    } else {
+        // two-shot / NVLS: this rank owns [lo, hi) of the slice
+        const size_t lo = n4 * size_t(rank) / world, hi = n4 * size_t(rank + 1) / world;
+        if (algo == B200CNN_ALGO_NVLS) {
+            const float4* mg = reinterpret_cast<const float4*>(v.mc_region + v.grads_off[parity]) + off4;
+            float4* mw = reinterpret_cast<float4*>(v.mc_region + v.params_off) + off4;
+            float4* mgw = reinterpret_cast<float4*>(v.mc_region + v.grads_off[parity]) + off4;
+            for (size_t i = lo + tid; i < hi; i += nthreads) {
+                const float4 s = multimem_ld_reduce_add(mg + i);
+                if (op == kOpSgd) {
+                    float4 w = w_local[i];
+                    w.x -= lr * s.x;
+                    w.y -= lr * s.y;
+                    w.z -= lr * s.z;
+                    w.w -= lr * s.w;
+                    multimem_st(mw + i, w);
+                } else {
+                    multimem_st(mgw + i, s);
+                }
+            }
+        } else {
+            for (size_t i = lo + tid; i < hi; i += nthreads) {
+                const float4 s = reduce_ranks<W>(g, world, i);
+                float4 out = s;
+                if (op == kOpSgd) {
+                    out = w_local[i];
+                    out.x -= lr * s.x;
+                    out.y -= lr * s.y;
+                    out.z -= lr * s.z;
+                    out.w -= lr * s.w;
+                }
+                const size_t dst_off = (op == kOpSgd) ? v.params_off : v.grads_off[parity];
+#pragma unroll
+                for (int k = 0; k < kMaxRanks; k++)
+                    if (k < world) st_peer(reinterpret_cast<float4*>(v.region[k] + dst_off) + off4 + i, out);
+            }
+        }
+        need_exit_barrier = true;  // all shards must have landed everywhere before anyone moves on
+    }
+    if (need_exit_barrier) signal_and_wait(v, rank, 1, seq);
+    if (threadIdx.x == 0) *seq_slot = seq;
+}
+
+int pick_blocks(size_t n4, int max_blocks) {
+    // ~4 float4 per thread per block before adding blocks: launch + flag latency dominates small slices.
+    size_t b = (n4 + size_t(kCommThreads) * 4 - 1) / (size_t(kCommThreads) * 4);
+    if (max_blocks <= 0 || max_blocks > kMaxBlocks) max_blocks = kMaxBlocks;
+    if (b < 1) b = 1;
+    if (b > size_t(max_blocks)) b = size_t(max_blocks);
+    return int(b);
+}
+
+}  // namespace
+}  // namespace b200cnn
+
+using namespace b200cnn;
+
+struct b200cnn_comm {
+    CommView view{};
+    size_t flat_floats = 0;
+    int algo = B200CNN_ALGO_AUTO;
+    int parity = 0;
+    uint32_t* local = nullptr;  // seq counters + error flag
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool forked = false;
+};
+
+namespace {
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int resolve_algo(const b200cnn_comm* c, int algo, size_t count, int op) {
+    if (algo == B200CNN_ALGO_AUTO) algo = c->algo;
+    if (c->view.world == 1) return B200CNN_ALGO_ONE_SHOT;
+    if (algo == B200CNN_ALGO_AUTO) {
+        if (count * sizeof(float) <= 256 * 1024) algo = B200CNN_ALGO_ONE_SHOT;
+        else algo = c->view.mc_region ? B200CNN_ALGO_NVLS : B200CNN_ALGO_TWO_SHOT;
+    }
+    if (algo == B200CNN_ALGO_NVLS && !c->view.mc_region) algo = B200CNN_ALGO_TWO_SHOT;
+    // The in-place one-shot all-reduce keeps at most 4 float4 per thread in registers.
+    if (op == kOpReduceOnly && algo == B200CNN_ALGO_ONE_SHOT &&
+        count / 4 > size_t(kMaxBlocks) * kCommThreads * 4)
+        algo = B200CNN_ALGO_TWO_SHOT;
+    return algo;
+}
+
+int launch(const CommView& v, int ranks_y, size_t off4, size_t n4, const float* lr_dev, float lr, int algo, int parity,
+           int op, int root, int blocks, cudaStream_t st) {
+    const dim3 grid(blocks, ranks_y);
+#define B200CNN_LAUNCH_W(W) allreduce_kernel<W><<<grid, kCommThreads, 0, st>>>(v, off4, n4, lr_dev, lr, algo, parity, op, root)
+    switch (v.world) {
+        case 1: B200CNN_LAUNCH_W(1); break;
+        case 2: B200CNN_LAUNCH_W(2); break;
+        case 4: B200CNN_LAUNCH_W(4); break;
+        case 8: B200CNN_LAUNCH_W(8); break;
+        default: B200CNN_LAUNCH_W(0); break;
+    }
+#undef B200CNN_LAUNCH_W
+    B200CNN_CHECK_LAUNCH("allreduce_sgd");
+    return 0;
+}
+
+int enqueue(b200cnn_comm* c, size_t offset, size_t count, const float* lr_dev, float lr, int algo, int parity, int op,
+            int root, int max_blocks, cudaStream_t st) {
+    if ((offset | count) & 3) return set_error(kInvalidValue, "comm: offset and count must be multiples of 4 floats");
+    if (offset + count > c->flat_floats) return set_error(kInvalidValue, "comm: slice [%zu, %zu) outside the %zu-float buffer", offset, offset + count, c->flat_floats);
+    if (parity != 0 && parity != 1) return set_error(kInvalidValue, "comm: parity must be 0 or 1");
+    algo = resolve_algo(c, algo, count, op);
+    const size_t n4 = count / 4;
+    int blocks = pick_blocks(n4, max_blocks);
+    if (op == kOpReduceOnly && algo == B200CNN_ALGO_ONE_SHOT) {
+        // registers hold the results across the barrier: make sure 4 per thread is enough
+        const size_t need = (n4 + size_t(kCommThreads) * 4 - 1) / (size_t(kCommThreads) * 4);
+        if (size_t(blocks) < need) blocks = int(need);
+    }
+    return launch(c->view, 1, offset / 4, n4, lr_dev, lr, algo, parity, op, root, blocks, st);
+}
+
+}  // namespace
+
+extern "C" size_t b200cnn_comm_params_offset(size_t) { return B200CNN_COMM_FLAG_BYTES; }
+extern "C" size_t b200cnn_comm_grads_offset(size_t flat_floats, int parity) {
+    const size_t buf = align_up(flat_floats * sizeof(float), 4096);
+    return B200CNN_COMM_FLAG_BYTES + buf * size_t(1 + (parity ? 1 : 0));
+}
+extern "C" size_t b200cnn_comm_region_bytes(size_t flat_floats) {
+    return B200CNN_COMM_FLAG_BYTES + 3 * align_up(flat_floats * sizeof(float), 4096);
+}
+
+extern "C" b200cnn_comm* b200cnn_comm_create(int rank, int world, void* const* region_ptrs, void* multicast_ptr,
+                                             size_t flat_floats) {
+    if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world || !region_ptrs || flat_floats == 0 || (flat_floats & 3)) {
+        set_error(kInvalidValue, "comm_create: need 1 <= world <= %d, 0 <= rank < world, flat_floats %% 4 == 0", kMaxRanks);
+        return nullptr;
+    }
+    auto* c = new (std::nothrow) b200cnn_comm;
+    if (!c) return nullptr;
+    c->flat_floats = flat_floats;
+    c->view.rank = rank;
+    c->view.world = world;
+    c->view.emulate = 0;
+    for (int r = 0; r < kMaxRanks; r++) c->view.region[r] = static_cast<char*>(region_ptrs[r < world ? r : rank]);
+    c->view.mc_region = static_cast<char*>(multicast_ptr);
+    c->view.params_off = b200cnn_comm_params_offset(flat_floats);
+    c->view.grads_off[0] = b200cnn_comm_grads_offset(flat_floats, 0);
+    c->view.grads_off[1] = b200cnn_comm_grads_offset(flat_floats, 1);
+    const size_t local_bytes = (kMaxBlocks + 16) * sizeof(uint32_t);
+    if (cudaMalloc(&c->local, local_bytes) != cudaSuccess || cudaMemset(c->local, 0, local_bytes) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+        set_error(int(cudaGetLastError()), "comm_create: CUDA resource creation failed");
+        delete c;
+        return nullptr;
+    }
+    c->view.seq = c->local;
+    c->view.errflag = c->local + kMaxBlocks;
+    return c;
+}
+
+extern "C" void b200cnn_comm_destroy(b200cnn_comm* c) {
+    if (!c) return;
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->local) cudaFree(c->local);
+    delete c;
+}
+
+extern "C" int b200cnn_comm_rank(const b200cnn_comm* c) { return c->view.rank; }
+extern "C" int b200cnn_comm_world(const b200cnn_comm* c) { return c->view.world; }
+extern "C" int b200cnn_comm_has_multicast(const b200cnn_comm* c) { return c->view.mc_region != nullptr; }
+extern "C" float* b200cnn_comm_params(b200cnn_comm* c) {
+    return reinterpret_cast<float*>(c->view.region[c->view.rank] + c->view.params_off);
+}
+extern "C" float* b200cnn_comm_grads(b200cnn_comm* c, int parity) {
+    return reinterpret_cast<float*>(c->view.region[c->view.rank] + c->view.grads_off[parity ? 1 : 0]);
+}
+extern "C" int b200cnn_comm_set_algo(b200cnn_comm* c, int algo) {
+    if (algo < B200CNN_ALGO_AUTO || algo > B200CNN_ALGO_NVLS) return set_error(kInvalidValue, "comm_set_algo: unknown algorithm %d", algo);
+    if (algo == B200CNN_ALGO_NVLS && !c->view.mc_region) return set_error(kInvalidValue, "comm_set_algo: no multicast mapping on this communicator");
+    c->algo = algo;
+    return 0;
+}
+extern "C" int b200cnn_comm_error(b200cnn_comm* c) {
+    uint32_t flag = 0;
+    if (cudaMemcpy(&flag, c->view.errflag, sizeof(flag), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return int(flag);
+}
+
+extern "C" int b200cnn_comm_allreduce_sgd(b200cnn_comm* c, size_t offset, size_t count, float lr, int algo, int parity,
+                                          int max_blocks, b200cnn_stream stream) {
+    return enqueue(c, offset, count, nullptr, lr, algo, parity, kOpSgd, 0, max_blocks, as_stream(stream));
+}
+extern "C" int b200cnn_comm_allreduce(b200cnn_comm* c, size_t offset, size_t count, int algo, int parity,
+                                      int max_blocks, b200cnn_stream stream) {
+    return enqueue(c, offset, count, nullptr, 0.0f, algo, parity, kOpReduceOnly, 0, max_blocks, as_stream(stream));
+}
+extern "C" int b200cnn_comm_broadcast_params(b200cnn_comm* c, int root, b200cnn_stream stream) {
+    if (root < 0 || root >= c->view.world) return set_error(kInvalidValue, "comm_broadcast_params: bad root %d", root);
+    return enqueue(c, 0, c->flat_floats, nullptr, 0.0f, B200CNN_ALGO_ONE_SHOT, 0, kOpBroadcast, root, 32, as_stream(stream));
+}
+extern "C" int b200cnn_comm_barrier(b200cnn_comm* c, b200cnn_stream stream) {
+    return launch(c->view, 1, 0, 0, nullptr, 0.0f, B200CNN_ALGO_ONE_SHOT, 0, kOpBarrier, 0, 1, as_stream(stream));
+}
+
+extern "C" int b200cnn_comm_emulate_allreduce_sgd(int world, void* const* region_ptrs, size_t flat_floats, size_t offset,
+                                                  size_t count, float lr, int algo, int parity, int blocks,
+                                                  uint32_t* seq_scratch, b200cnn_stream stream) {
+    if (world < 1 || world > kMaxRanks || (offset | count) & 3 || offset + count > flat_floats)
+        return set_error(kInvalidValue, "comm_emulate: bad arguments");
+    if (algo != B200CNN_ALGO_ONE_SHOT && algo != B200CNN_ALGO_TWO_SHOT)
+        return set_error(kInvalidValue, "comm_emulate: only one-shot and two-shot can run without a switch");
+    if (blocks < 1 || blocks * world > 148) return set_error(kInvalidValue, "comm_emulate: blocks*world must fit one wave (<= 148)");
+    CommView v{};
+    v.world = world;
+    v.emulate = 1;
+    for (int r = 0; r < kMaxRanks; r++) v.region[r] = static_cast<char*>(region_ptrs[r < world ? r : 0]);
+    v.params_off = b200cnn_comm_params_offset(flat_floats);
+    v.grads_off[0] = b200cnn_comm_grads_offset(flat_floats, 0);
+    v.grads_off[1] = b200cnn_comm_grads_offset(flat_floats, 1);
+    v.seq = seq_scratch;                               // [world][kMaxBlocks]
+    v.errflag = seq_scratch + size_t(world) * kMaxBlocks;  // + 1 word
+    return launch(v, world, offset / 4, count / 4, nullptr, lr, algo, parity, kOpSgd, 0, blocks, as_stream(stream));
+}
+
+// ---- engine hooks ---------------------------------------------------------------------------
+namespace b200cnn {
+
+int comm_allreduce_sgd_slice(b200cnn_comm* c, size_t offset, size_t count, const float* lr_dev, cudaStream_t after) {
+    B200CNN_CUDA(cudaEventRecord(c->ev_fork, after));
+    B200CNN_CUDA(cudaStreamWaitEvent(c->stream, c->ev_fork, 0));
+    c->forked = true;
+    return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, 16, c->stream);
+}
+
+int comm_join(b200cnn_comm* c, cudaStream_t st) {
+    if (!c->forked) return 0;
+    B200CNN_CUDA(cudaEventRecord(c->ev_join, c->stream));
+    B200CNN_CUDA(cudaStreamWaitEvent(st, c->ev_join, 0));
+    c->forked = false;
+    return 0;
+}
+
+float* comm_current_grads(b200cnn_comm* c) { return b200cnn_comm_grads(c, c->parity); }
+void comm_flip_parity(b200cnn_comm* c) { c->parity ^= 1; }
+int comm_parity(const b200cnn_comm* c) { return c->parity; }
+
+}  // namespace b200cnn

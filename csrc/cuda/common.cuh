@@ -1,0 +1,55 @@
+// Shared host/device helpers for the sm_100a library.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+
+#include "b200cnn.h"
+
+namespace b200cnn {
+
+// Records the message returned by b200cnn_last_error(); returns `code` for `return set_error(...)`.
+int set_error(int code, const char* fmt, ...);
+
+inline cudaStream_t as_stream(b200cnn_stream s) { return static_cast<cudaStream_t>(s); }
+
+// After a kernel launch: pick up launch-configuration errors without synchronising.
+#define B200CNN_CHECK_LAUNCH(name)                                                              \
+    do {                                                                                        \
+        cudaError_t e__ = cudaGetLastError();                                                   \
+        if (e__ != cudaSuccess) return ::b200cnn::set_error(int(e__), "%s: %s", name, cudaGetErrorString(e__)); \
+    } while (0)
+
+#define B200CNN_CUDA(call)                                                                      \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess)                                                                 \
+            return ::b200cnn::set_error(int(e__), "%s failed: %s", #call, cudaGetErrorString(e__)); \
+    } while (0)
+
+constexpr int kInvalidValue = 1;  // cudaErrorInvalidValue
+
+__host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// Derivative of an activation expressed through its OUTPUT value, like the reference's
+// tanh_g / relu_g (cnn.c:51-57).
+__device__ __forceinline__ float act_grad_from_output(int act, float y) {
+    if (act == B200CNN_ACT_TANH) return 1.0f - y * y;
+    if (act == B200CNN_ACT_RELU) return y > 0.0f ? 1.0f : 0.0f;
+    return 1.0f;
+}
+
+__device__ __forceinline__ float apply_act(int act, float v) {
+    if (act == B200CNN_ACT_TANH) return tanhf(v);
+    if (act == B200CNN_ACT_RELU) return v > 0.0f ? v : 0.0f;
+    return v;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace b200cnn

@@ -1,0 +1,507 @@
+// Training engine: owns the device-side state of one network replica and runs whole mini-batches.
+//
+// It replaces the per-sample driver of the reference — Layer_setInputs, Layer_learnOutputs,
+// Layer_getErrorTotal and Layer_update called from main() once per image
+// (/root/reference/cnn.c:451-474, same loop in CUDAcnn.cu:451-480) — by a fixed launch sequence over
+// a batch, optionally captured as one CUDA graph so a step costs one launch on the host.
+//
+// Memory: all parameters live in ONE flat fp32 buffer and all gradients in another, each tensor
+// starting on a 128-byte boundary.  The single-GPU update is one kernel over the flat buffer; the
+// data-parallel path binds NVLink-mapped symmetric buffers (b200cnn_engine_bind_buffers) and runs the
+// fused all-reduce + SGD kernel per layer slice instead.
+#include <cstring>
+#include <vector>
+
+#include "backend.cuh"
+#include "common.cuh"
+#include "../comm/comm.cuh"
+#include "b200cnn_comm.h"
+
+namespace b200cnn {
+
+constexpr size_t kAlignFloats = 32;  // 128 B
+static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct EngineLayer {
+    b200cnn_layer_desc d{};
+    int nnodes = 0;
+    int act = B200CNN_ACT_NONE;
+    long w_off = -1, b_off = -1;
+    long nw = 0, nb = 0;
+    float* a = nullptr;     // activations  [max_batch][ld]
+    float* dz = nullptr;    // d loss / d pre-activation [max_batch][ld]
+    int32_t* argmax = nullptr;
+    int ld = 0;             // row stride of a / dz (nnodes, except the padded softmax layer)
+};
+
+}  // namespace b200cnn
+
+using namespace b200cnn;
+
+struct b200cnn_engine {
+    std::vector<EngineLayer> layers;
+    int max_batch = 0;
+    size_t dense_params = 0, flat_floats = 0;
+    float* params = nullptr;
+    float* grads = nullptr;
+    bool own_buffers = false;
+    void* arena = nullptr;       // activations, dz, scratch, metrics, hyper-parameters
+    float* scratch = nullptr;
+    size_t scratch_bytes = 0;
+    float* metrics = nullptr;    // [4]
+    float* lr_dev = nullptr;     // [1], read by the graph-captured update
+    float lr_host_cached = -1.0f;
+    // last forward
+    const void* last_images = nullptr;
+    int last_is_u8 = 0;
+    int last_batch = 0;
+    // graph cache (one entry: the training loop reuses the same staging buffers every step)
+    cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};  // one per gradient-buffer parity
+    const void* g_images = nullptr;
+    const uint8_t* g_labels = nullptr;
+    int g_batch = 0, g_is_u8 = 0;
+    cudaStream_t g_stream = nullptr;
+    b200cnn_comm* comm = nullptr;
+    int launches_per_step = 0;
+};
+
+namespace {
+
+// Gradient buffer of the step being enqueued: the communicator's double buffer when attached.
+float* cur_grads(b200cnn_engine* e) { return e->comm ? comm_current_grads(e->comm) : e->grads; }
+
+b200cnn_conv_shape conv_shape(const EngineLayer& prev, const EngineLayer& l, int batch) {
+    b200cnn_conv_shape s;
+    s.n = batch;
+    s.c = prev.d.depth;
+    s.h = prev.d.height;
+    s.w = prev.d.width;
+    s.oc = l.d.depth;
+    s.oh = l.d.height;
+    s.ow = l.d.width;
+    s.k = l.d.k;
+    s.pad = l.d.pad;
+    s.stride = l.d.stride;
+    return s;
+}
+
+int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
+                    cudaStream_t st, int* launches) {
+    auto& L = e->layers;
+    for (size_t li = 1; li < L.size(); li++) {
+        EngineLayer& l = L[li];
+        const EngineLayer& p = L[li - 1];
+        const void* in = (li == 1) ? images : static_cast<const void*>(p.a);
+        const int in_u8 = (li == 1) ? is_u8 : 0;
+        int rc = 0;
+        switch (l.d.type) {
+            case B200CNN_LAYER_CONV: {
+                const b200cnn_conv_shape s = conv_shape(p, l, batch);
+                rc = b200cnn_conv2d_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, l.a, &s, l.act, st);
+                break;
+            }
+            case B200CNN_LAYER_POOL:
+                if (in_u8) return set_error(kInvalidValue, "engine: a pool layer cannot read uint8 input directly");
+                rc = b200cnn_maxpool_fwd(static_cast<const float*>(in), l.a, l.argmax, batch, p.d.depth, p.d.height,
+                                         p.d.width, l.d.k, l.d.stride, st);
+                break;
+            case B200CNN_LAYER_FULL:
+                if (in_u8) return set_error(kInvalidValue, "engine: a full layer cannot read uint8 input directly");
+                rc = b200cnn_linear_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a,
+                                        batch, l.nnodes, p.nnodes, l.ld, l.act, st);
+                break;
+            default: return set_error(kInvalidValue, "engine: bad layer type %d", l.d.type);
+        }
+        if (rc) return rc;
+        if (launches) (*launches)++;
+    }
+    // Softmax over the last layer's logits, in place; with labels also dz and the metrics.
+    EngineLayer& out = L.back();
+    const int rc = b200cnn_softmax_xent(out.a, labels, out.a, labels ? out.dz : nullptr, labels ? e->metrics : nullptr,
+                                        batch, out.nnodes, out.ld, st);
+    if (rc) return rc;
+    if (launches) (*launches)++;
+    return 0;
+}
+
+// Per-layer hook after that layer's gradients are complete: the data-parallel path launches the fused
+// all-reduce + SGD for the layer's slice right here so it overlaps the rest of backward.
+int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, cudaStream_t st, int* launches) {
+    if (!e->comm) return 0;
+    const long begin = l.w_off;
+    const long end = l.b_off + long(round_up(size_t(l.nb), kAlignFloats));
+    const int rc = comm_allreduce_sgd_slice(e->comm, size_t(begin), size_t(end - begin), e->lr_dev, st);
+    if (rc) return rc;
+    if (launches) (*launches)++;
+    return 0;
+}
+
+int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch, cudaStream_t st, int* launches) {
+    auto& L = e->layers;
+    float* grads = cur_grads(e);
+    for (size_t li = L.size() - 1; li >= 1; li--) {
+        EngineLayer& l = L[li];
+        EngineLayer& p = L[li - 1];
+        const void* in = (li == 1) ? images : static_cast<const void*>(p.a);
+        const int in_u8 = (li == 1) ? is_u8 : 0;
+        int rc = 0;
+        switch (l.d.type) {
+            case B200CNN_LAYER_FULL:
+                // Data gradient first: once the layer's update is launched (two-shot / NVLS variants) a
+                // peer may overwrite this layer's weights, so nothing may read them afterwards.
+                if (li > 1) {
+                    rc = b200cnn_linear_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, batch, l.nnodes,
+                                                 p.nnodes, l.ld, st);
+                    if (rc) return rc;
+                    if (launches) (*launches)++;
+                }
+                rc = b200cnn_linear_bwd_weight(l.dz, static_cast<const float*>(in), grads + l.w_off, grads + l.b_off,
+                                               0, batch, l.nnodes, p.nnodes, l.ld, st);
+                if (rc) return rc;
+                if (launches) (*launches)++;
+                if ((rc = layer_grads_ready(e, l, st, launches))) return rc;
+                break;
+            case B200CNN_LAYER_CONV: {
+                const b200cnn_conv_shape s = conv_shape(p, l, batch);
+                if (li > 1) {
+                    rc = b200cnn_conv2d_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, &s, st);
+                    if (rc) return rc;
+                    if (launches) (*launches)++;
+                }
+                rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0, e->scratch, &s, st);
+                if (rc) return rc;
+                if (launches) (*launches) += 2;
+                if ((rc = layer_grads_ready(e, l, st, launches))) return rc;
+                break;
+            }
+            case B200CNN_LAYER_POOL:
+                if (li > 1) {
+                    rc = b200cnn_maxpool_bwd(l.dz, l.argmax, p.a, p.act, p.dz, batch, p.d.depth, p.d.height, p.d.width,
+                                             l.d.k, l.d.stride, st);
+                    if (rc) return rc;
+                    if (launches) (*launches)++;
+                }
+                break;
+            default: return set_error(kInvalidValue, "engine: bad layer type %d", l.d.type);
+        }
+    }
+    return 0;
+}
+
+__global__ void sgd_dev_lr_kernel(float* __restrict__ w, const float* __restrict__ g, size_t n4,
+                                  const float* __restrict__ lr_dev) {
+    const float lr = *lr_dev;
+    float4* w4 = reinterpret_cast<float4*>(w);
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
+        float4 a = w4[i];
+        const float4 d = g4[i];
+        a.x -= lr * d.x;
+        a.y -= lr * d.y;
+        a.z -= lr * d.z;
+        a.w -= lr * d.w;
+        w4[i] = a;
+    }
+}
+
+int enqueue_update(b200cnn_engine* e, cudaStream_t st, int* launches) {
+    if (e->comm) return comm_join(e->comm, st);  // per-layer fused updates already enqueued
+    const size_t n4 = e->flat_floats / 4;
+    const int blocks = int(std::min<size_t>((n4 + 255) / 256, 148 * 4));
+    sgd_dev_lr_kernel<<<blocks, 256, 0, st>>>(e->params, cur_grads(e), n4, e->lr_dev);
+    B200CNN_CHECK_LAUNCH("engine sgd");
+    if (launches) (*launches)++;
+    return 0;
+}
+
+int set_lr(b200cnn_engine* e, float lr, cudaStream_t st) {
+    if (lr == e->lr_host_cached) return 0;
+    // A 4-byte pageable copy is staged by the runtime, so `lr` may go out of scope immediately.
+    B200CNN_CUDA(cudaMemcpyAsync(e->lr_dev, &lr, sizeof(float), cudaMemcpyHostToDevice, st));
+    e->lr_host_cached = lr;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layers, int nlayers, int max_batch) {
+    if (!layers || nlayers < 2 || max_batch < 1 || layers[0].type != B200CNN_LAYER_INPUT ||
+        layers[nlayers - 1].type != B200CNN_LAYER_FULL) {
+        set_error(kInvalidValue, "engine_create: need input ... full layers and max_batch >= 1");
+        return nullptr;
+    }
+    auto* e = new b200cnn_engine;
+    e->max_batch = max_batch;
+    size_t off = 0, arena_floats = 0, scratch_bytes = 0;
+    for (int i = 0; i < nlayers; i++) {
+        EngineLayer l;
+        l.d = layers[i];
+        l.nnodes = l.d.depth * l.d.width * l.d.height;
+        l.ld = l.nnodes;
+        if (i > 0) {
+            const EngineLayer& p = e->layers.back();
+            if (l.d.type == B200CNN_LAYER_CONV) {
+                l.nw = long(l.d.depth) * p.d.depth * l.d.k * l.d.k;
+                l.nb = l.d.depth;
+                l.act = B200CNN_ACT_RELU;
+                b200cnn_conv_shape s = conv_shape(p, l, max_batch);
+                scratch_bytes = std::max(scratch_bytes, b200cnn_conv2d_bwd_weight_scratch_bytes(&s));
+            } else if (l.d.type == B200CNN_LAYER_FULL) {
+                l.nw = long(l.nnodes) * p.nnodes;
+                l.nb = l.nnodes;
+                l.act = (i == nlayers - 1) ? B200CNN_ACT_NONE : B200CNN_ACT_TANH;
+                if (i == nlayers - 1) l.ld = int(round_up(size_t(l.nnodes), 16));  // 64-byte rows for the logits
+            } else if (l.d.type == B200CNN_LAYER_POOL) {
+                if (l.d.depth != p.d.depth) {
+                    set_error(kInvalidValue, "engine_create: pool layer %d changes depth", i);
+                    delete e;
+                    return nullptr;
+                }
+            }
+            if (l.nw) {
+                l.w_off = long(off);
+                off += round_up(size_t(l.nw), kAlignFloats);
+                l.b_off = long(off);
+                off += round_up(size_t(l.nb), kAlignFloats);
+                e->dense_params += size_t(l.nw + l.nb);
+            }
+        }
+        arena_floats += 2 * round_up(size_t(max_batch) * l.ld, kAlignFloats);
+        if (l.d.type == B200CNN_LAYER_POOL) arena_floats += round_up(size_t(max_batch) * l.nnodes, kAlignFloats);
+        e->layers.push_back(l);
+    }
+    e->flat_floats = off;
+    e->scratch_bytes = round_up(scratch_bytes, 512);
+    const size_t arena_bytes = arena_floats * sizeof(float) + e->scratch_bytes + 1024;
+    if (cudaMalloc(&e->arena, arena_bytes) != cudaSuccess || cudaMemset(e->arena, 0, arena_bytes) != cudaSuccess) {
+        set_error(int(cudaGetLastError()), "engine_create: cannot allocate %zu bytes of activations", arena_bytes);
+        delete e;
+        return nullptr;
+    }
+    float* cur = static_cast<float*>(e->arena);
+    for (EngineLayer& l : e->layers) {
+        l.a = cur;
+        cur += round_up(size_t(max_batch) * l.ld, kAlignFloats);
+        l.dz = cur;
+        cur += round_up(size_t(max_batch) * l.ld, kAlignFloats);
+        if (l.d.type == B200CNN_LAYER_POOL) {
+            l.argmax = reinterpret_cast<int32_t*>(cur);
+            cur += round_up(size_t(max_batch) * l.nnodes, kAlignFloats);
+        }
+    }
+    e->scratch = cur;
+    cur += e->scratch_bytes / sizeof(float);
+    e->metrics = cur;
+    e->lr_dev = cur + 8;
+    return e;
+}
+
+extern "C" void b200cnn_engine_destroy(b200cnn_engine* e) {
+    if (!e) return;
+    for (cudaGraphExec_t g : e->graph_exec)
+        if (g) cudaGraphExecDestroy(g);
+    if (e->own_buffers) {
+        cudaFree(e->params);
+        cudaFree(e->grads);
+    }
+    cudaFree(e->arena);
+    delete e;
+}
+
+extern "C" size_t b200cnn_engine_num_params(const b200cnn_engine* e) { return e->dense_params; }
+extern "C" size_t b200cnn_engine_flat_floats(const b200cnn_engine* e) { return e->flat_floats; }
+
+extern "C" void b200cnn_engine_param_layout(const b200cnn_engine* e, long* offsets, long* sizes) {
+    for (size_t i = 0; i < e->layers.size(); i++) {
+        const EngineLayer& l = e->layers[i];
+        offsets[2 * i] = l.w_off;
+        offsets[2 * i + 1] = l.b_off;
+        sizes[2 * i] = l.nw;
+        sizes[2 * i + 1] = l.nb;
+    }
+}
+
+static int ensure_buffers(b200cnn_engine* e) {
+    if (e->params) return 0;
+    const size_t bytes = e->flat_floats * sizeof(float);
+    B200CNN_CUDA(cudaMalloc(&e->params, bytes));
+    B200CNN_CUDA(cudaMalloc(&e->grads, bytes));
+    B200CNN_CUDA(cudaMemset(e->params, 0, bytes));
+    B200CNN_CUDA(cudaMemset(e->grads, 0, bytes));
+    e->own_buffers = true;
+    return 0;
+}
+
+extern "C" int b200cnn_engine_bind_buffers(b200cnn_engine* e, float* params, float* grads) {
+    if (e->params) return set_error(kInvalidValue, "engine_bind_buffers: buffers already in use");
+    if (!params || !grads || ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 127))
+        return set_error(kInvalidValue, "engine_bind_buffers: need two 128-byte aligned device buffers");
+    e->params = params;
+    e->grads = grads;
+    e->own_buffers = false;
+    return 0;
+}
+
+extern "C" float* b200cnn_engine_params(b200cnn_engine* e) { return ensure_buffers(e) ? nullptr : e->params; }
+extern "C" float* b200cnn_engine_grads(b200cnn_engine* e) { return ensure_buffers(e) ? nullptr : e->grads; }
+
+static int dense_transfer(b200cnn_engine* e, float* dev_flat, float* dense, bool to_device) {
+    if (int rc = ensure_buffers(e)) return rc;
+    std::vector<float> flat(e->flat_floats, 0.0f);
+    if (!to_device) B200CNN_CUDA(cudaMemcpy(flat.data(), dev_flat, flat.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    size_t d = 0;
+    for (const EngineLayer& l : e->layers) {
+        if (!l.nw) continue;
+        if (to_device) {
+            std::memcpy(&flat[l.w_off], dense + d, l.nw * sizeof(float));
+            std::memcpy(&flat[l.b_off], dense + d + l.nw, l.nb * sizeof(float));
+        } else {
+            std::memcpy(dense + d, &flat[l.w_off], l.nw * sizeof(float));
+            std::memcpy(dense + d + l.nw, &flat[l.b_off], l.nb * sizeof(float));
+        }
+        d += size_t(l.nw + l.nb);
+    }
+    if (to_device) B200CNN_CUDA(cudaMemcpy(dev_flat, flat.data(), flat.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+extern "C" int b200cnn_engine_set_params(b200cnn_engine* e, const float* dense_host) {
+    return dense_transfer(e, e->params ? e->params : b200cnn_engine_params(e), const_cast<float*>(dense_host), true);
+}
+extern "C" int b200cnn_engine_get_params(b200cnn_engine* e, float* dense_host) {
+    return dense_transfer(e, b200cnn_engine_params(e), dense_host, false);
+}
+extern "C" int b200cnn_engine_get_grads(b200cnn_engine* e, float* dense_host) {
+    if (int rc = ensure_buffers(e)) return rc;
+    return dense_transfer(e, cur_grads(e), dense_host, false);
+}
+
+extern "C" int b200cnn_engine_forward(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels,
+                                      int batch, b200cnn_stream stream) {
+    if (batch < 1 || batch > e->max_batch) return set_error(kInvalidValue, "engine_forward: batch %d outside [1, %d]", batch, e->max_batch);
+    if (int rc = ensure_buffers(e)) return rc;
+    e->last_images = images;
+    e->last_is_u8 = x_is_u8;
+    e->last_batch = batch;
+    return enqueue_forward(e, images, x_is_u8, labels, batch, as_stream(stream), nullptr);
+}
+
+extern "C" int b200cnn_engine_backward(b200cnn_engine* e, b200cnn_stream stream) {
+    if (!e->last_batch) return set_error(kInvalidValue, "engine_backward: no forward pass to differentiate");
+    b200cnn_comm* saved = e->comm;
+    e->comm = nullptr;  // plain backward never communicates
+    const int rc = enqueue_backward(e, e->last_images, e->last_is_u8, e->last_batch, as_stream(stream), nullptr);
+    e->comm = saved;
+    return rc;
+}
+
+extern "C" int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream stream) {
+    if (int rc = ensure_buffers(e)) return rc;
+    if (int rc = set_lr(e, lr, as_stream(stream))) return rc;
+    b200cnn_comm* saved = e->comm;
+    e->comm = nullptr;
+    const int rc = enqueue_update(e, as_stream(stream), nullptr);
+    e->comm = saved;
+    return rc;
+}
+
+static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
+                        cudaStream_t st, int* launches) {
+    if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches)) return rc;
+    if (int rc = enqueue_backward(e, images, is_u8, batch, st, launches)) return rc;
+    return enqueue_update(e, st, launches);
+}
+
+extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels,
+                                         int batch, float lr, int use_graph, b200cnn_stream stream) {
+    if (batch < 1 || batch > e->max_batch) return set_error(kInvalidValue, "engine_train_step: batch %d outside [1, %d]", batch, e->max_batch);
+    if (!labels) return set_error(kInvalidValue, "engine_train_step: labels are required");
+    if (int rc = ensure_buffers(e)) return rc;
+    cudaStream_t st = as_stream(stream);
+    if (int rc = set_lr(e, lr, st)) return rc;
+    e->last_images = images;
+    e->last_is_u8 = x_is_u8;
+    e->last_batch = batch;
+    // Data-parallel: this step's gradients go to the other half of the double buffer, so peers that
+    // are still reading the previous step's gradients are never overwritten.
+    if (e->comm) comm_flip_parity(e->comm);
+    const int par = e->comm ? comm_parity(e->comm) : 0;
+    if (!use_graph) {
+        int launches = 0;
+        const int rc = enqueue_step(e, images, x_is_u8, labels, batch, st, &launches);
+        e->launches_per_step = launches;
+        return rc;
+    }
+    const bool same_key = e->g_images == images && e->g_labels == labels && e->g_batch == batch &&
+                          e->g_is_u8 == x_is_u8 && e->g_stream == st;
+    if (!same_key) {
+        for (cudaGraphExec_t& g : e->graph_exec)
+            if (g) {
+                cudaGraphExecDestroy(g);
+                g = nullptr;
+            }
+    }
+    if (!e->graph_exec[par]) {
+        if (st == nullptr) return set_error(kInvalidValue, "engine_train_step: graph capture needs a non-default stream");
+        cudaGraph_t graph = nullptr;
+        B200CNN_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int launches = 0;
+        const int rc = enqueue_step(e, images, x_is_u8, labels, batch, st, &launches);
+        const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+        if (rc) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc;
+        }
+        if (ce != cudaSuccess) return set_error(int(ce), "engine_train_step: capture failed: %s", cudaGetErrorString(ce));
+        const cudaError_t ie = cudaGraphInstantiate(&e->graph_exec[par], graph, 0);
+        cudaGraphDestroy(graph);
+        if (ie != cudaSuccess) return set_error(int(ie), "engine_train_step: instantiate failed: %s", cudaGetErrorString(ie));
+        e->g_images = images;
+        e->g_labels = labels;
+        e->g_batch = batch;
+        e->g_is_u8 = x_is_u8;
+        e->g_stream = st;
+        e->launches_per_step = launches;
+    }
+    B200CNN_CUDA(cudaGraphLaunch(e->graph_exec[par], st));
+    return 0;
+}
+
+extern "C" float* b200cnn_engine_metrics(b200cnn_engine* e) { return e->metrics; }
+
+extern "C" int b200cnn_engine_reset_metrics(b200cnn_engine* e, b200cnn_stream stream) {
+    B200CNN_CUDA(cudaMemsetAsync(e->metrics, 0, 4 * sizeof(float), as_stream(stream)));
+    return 0;
+}
+
+extern "C" int b200cnn_engine_layer_output(b200cnn_engine* e, int layer, int batch, float* host) {
+    if (layer < 1 || layer >= int(e->layers.size()) || batch < 1 || batch > e->max_batch)
+        return set_error(kInvalidValue, "engine_layer_output: bad layer / batch");
+    const EngineLayer& l = e->layers[size_t(layer)];
+    B200CNN_CUDA(cudaMemcpy2D(host, l.nnodes * sizeof(float), l.a, l.ld * sizeof(float), l.nnodes * sizeof(float),
+                              size_t(batch), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int b200cnn_engine_launches_per_step(const b200cnn_engine* e) { return e->launches_per_step; }
+
+// Data-parallel hook (declared in comm.cuh): the communicator must have been created over this
+// engine's bound parameter / gradient buffers.
+extern "C" int b200cnn_engine_attach_comm(b200cnn_engine* e, b200cnn_comm* comm) {
+    for (cudaGraphExec_t& g : e->graph_exec)
+        if (g) {
+            cudaGraphExecDestroy(g);
+            g = nullptr;
+        }
+    if (!comm) {
+        e->comm = nullptr;
+        return 0;
+    }
+    if (e->params && e->params != b200cnn_comm_params(comm))
+        return set_error(kInvalidValue, "engine_attach_comm: attach before the engine allocates its own parameter buffers");
+    e->params = b200cnn_comm_params(comm);
+    e->grads = b200cnn_comm_grads(comm, 0);
+    e->own_buffers = false;
+    e->comm = comm;
+    return 0;
+}

@@ -1,0 +1,31 @@
+// Error reporting and build facts of the GPU library.
+#include <cstdarg>
+#include <cstdio>
+
+#include "common.cuh"
+
+namespace b200cnn {
+
+static thread_local char g_error[512] = "";
+
+int set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+    return code ? code : kInvalidValue;
+}
+
+}  // namespace b200cnn
+
+extern "C" const char* b200cnn_last_error(void) { return b200cnn::g_error; }
+
+extern "C" const char* b200cnn_build_info(void) {
+#define B200CNN_STR2(x) #x
+#define B200CNN_STR(x) B200CNN_STR2(x)
+    return "b200cnn cuda library; target sm_100a; CUDA " B200CNN_STR(CUDART_VERSION) "; features: "
+#ifdef B200CNN_HAVE_TCGEN05
+           "tcgen05-gemm tma "
+#endif
+           "simt p2p-allreduce-sgd nvls";
+}

@@ -1,0 +1,169 @@
+/* C ABI of the GPU library (libb200cnn_cuda.so), sm_100a only.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - tensors are fp32, activations NCHW / row-major [batch][features], conv weights
+ *     [out_c][in_c][ky][kx], FC weights [out][in] (the reference's layouts:
+ *     /root/reference/cnn.c:116-121, :181-197, :333);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - functions return 0 on success or a cudaError_t value; b200cnn_last_error() describes it;
+ *   - launchers only enqueue work, they never synchronise and never allocate.
+ *
+ * The reference has one GPU kernel (conv forward, fp64, batch 1: CUDAcnn.cu:167-195) and one host
+ * wrapper that re-allocates and re-uploads per call (CUDAcnn.cu:198-218).  Everything else below
+ * replaces code that the reference runs on the CPU.
+ */
+#ifndef B200CNN_H
+#define B200CNN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200cnn_stream;
+
+enum { B200CNN_ACT_NONE = 0, B200CNN_ACT_TANH = 1, B200CNN_ACT_RELU = 2 };
+
+const char* b200cnn_last_error(void);
+/* Compile-time facts, for tests and logs: "sm_100a", CUDA version, feature list. */
+const char* b200cnn_build_info(void);
+
+typedef struct b200cnn_conv_shape {
+    int n, c, h, w;        /* input  N,C,H,W */
+    int oc, oh, ow;        /* output channels and spatial size (passed in like Layer_create_conv, cnn.c:329) */
+    int k, pad, stride;    /* square kernel */
+} b200cnn_conv_shape;
+
+/* Which implementation the GEMM-shaped entry points use.  AUTO = tcgen05 when the shape qualifies
+ * (16-byte aligned row strides etc.), CUDA-core kernels otherwise.  Tests pin one or the other. */
+enum { B200CNN_BACKEND_AUTO = 0, B200CNN_BACKEND_SIMT = 1, B200CNN_BACKEND_TCGEN05 = 2 };
+int b200cnn_set_backend(int backend);
+int b200cnn_get_backend(void);
+
+/* ---- convolution (K1-K3) ------------------------------------------------------------------ */
+/* y = act(conv(x, w) + b).  If x_is_u8 the input is uint8 pixels scaled by 1/255 on the fly
+ * (fuses the reference's img[j]/255.0, cnn.c:457).  Replaces Layer_feedForw_conv (cnn.c:175-210)
+ * and conv_forward_kernel (CUDAcnn.cu:167-195). */
+int b200cnn_conv2d_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* y,
+                       const b200cnn_conv_shape* s, int act, b200cnn_stream stream);
+/* dx = conv_transpose(dz, w) * act'(a_prev) where a_prev is the activation that produced x
+ * (pass act_prev = NONE and a_prev = NULL for a raw input gradient).  Replaces the data half of
+ * Layer_feedBack_conv (cnn.c:235). */
+int b200cnn_conv2d_bwd_data(const float* dz, const float* w, const float* a_prev, int act_prev, float* dx,
+                            const b200cnn_conv_shape* s, b200cnn_stream stream);
+/* dw[oc][ic][ky][kx] (+)= sum_n,oy,ox dz * x ; db[oc] (+)= sum dz.  Two passes: per-chunk partial
+ * sums into `scratch`, then a fixed-order reduction (deterministic, no atomics).
+ * scratch must hold b200cnn_conv2d_bwd_weight_scratch_bytes(s) bytes.
+ * Replaces the weight half of Layer_feedBack_conv (cnn.c:236, :242). */
+size_t b200cnn_conv2d_bwd_weight_scratch_bytes(const b200cnn_conv_shape* s);
+int b200cnn_conv2d_bwd_weight(const float* dz, const void* x, int x_is_u8, float* dw, float* db, int accumulate,
+                              void* scratch, const b200cnn_conv_shape* s, b200cnn_stream stream);
+
+/* ---- fully connected (K4, K6) ------------------------------------------------------------- */
+/* y[m][n] = act(sum_k x[m][k] w[n][k] + b[n]); ldy = row stride of y in floats (>= n).
+ * Replaces Layer_feedForw_full (cnn.c:113-150). */
+int b200cnn_linear_fwd(const float* x, const float* w, const float* b, float* y, int m, int n, int k, int ldy,
+                       int act, b200cnn_stream stream);
+/* dx[m][k] = (sum_n dz[m][n] w[n][k]) * act'(a_prev[m][k]); lddz = row stride of dz. (cnn.c:166) */
+int b200cnn_linear_bwd_data(const float* dz, const float* w, const float* a_prev, int act_prev, float* dx, int m,
+                            int n, int k, int lddz, b200cnn_stream stream);
+/* dw[n][k] (+)= sum_m dz[m][n] x[m][k]; db[n] (+)= sum_m dz[m][n]. (cnn.c:167, :170) */
+int b200cnn_linear_bwd_weight(const float* dz, const float* x, float* dw, float* db, int accumulate, int m, int n,
+                              int k, int lddz, b200cnn_stream stream);
+
+/* ---- softmax + cross-entropy gradient + metrics (K5) -------------------------------------- */
+/* logits[m][ld] (first n columns valid) -> probs (optional, same stride), dz = probs - onehot(label)
+ * (columns n..ld-1 of dz are written as 0), and metrics[4] += {sum CE loss, sum MSE of (p - y) over
+ * n outputs (the reference's printed "error", cnn.c:275-282), #correct (first-max, cnn.c:508-513), m}.
+ * Replaces cnn.c:125-143 and :285-286. */
+int b200cnn_softmax_xent(const float* logits, const uint8_t* labels, float* probs, float* dz, float* metrics,
+                         int m, int n, int ld, b200cnn_stream stream);
+
+/* ---- max pooling (K7; not in the reference) ------------------------------------------------ */
+int b200cnn_maxpool_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride,
+                        b200cnn_stream stream);
+/* dx = route(dy) * act'(a_prev): a_prev (optional) is the pooled layer's input activation, so the
+ * result is the gradient w.r.t. the PRE-activation of the layer feeding the pool. */
+int b200cnn_maxpool_bwd(const float* dy, const int32_t* argmax, const float* a_prev, int act_prev, float* dx, int n,
+                        int c, int h, int w, int k, int stride, b200cnn_stream stream);
+
+/* ---- SGD (K8 with world size 1) ------------------------------------------------------------ */
+/* w -= lr * g; optionally g = 0.  Replaces Layer_update (cnn.c:303-311). */
+int b200cnn_sgd_update(float* w, float* g, size_t n, float lr, int zero_grad, b200cnn_stream stream);
+
+/* ---- synthetic data on the device (K10) ---------------------------------------------------- */
+/* Fills images[n][h*w] (uint8) and labels[n] with the same class-prototype + noise family as the
+ * CPU generator; counter-based, so any (seed, first_index) range can be produced independently. */
+int b200cnn_synthetic_batch(uint8_t* images, uint8_t* labels, int n, int h, int w, int nclass, uint64_t seed,
+                            uint64_t first_index, b200cnn_stream stream);
+
+/* Random mini-batch with replacement out of a device-resident data set (the reference draws
+ * index = rand() % train_size per sample, cnn.c:455): out_images[b] = images[idx_b], same for labels;
+ * idx_b is a counter-based hash of (seed, step, b). */
+int b200cnn_gather_batch(const uint8_t* images, const uint8_t* labels, uint32_t n_items, int item_bytes,
+                         uint8_t* out_images, uint8_t* out_labels, int batch, uint64_t seed, uint64_t step,
+                         uint32_t shard_begin, uint32_t shard_len, b200cnn_stream stream);
+
+/* ======== training engine ====================================================================
+ * A network is a list of layers like the reference's linked list of Layer nodes (cnn.c:15-43):
+ * input, conv (+ReLU), pool, full (+tanh; the last full layer is the softmax output).
+ * The engine owns activations / gradients for up to max_batch samples and runs a whole
+ * mini-batch per launch sequence; it replaces Layer_setInputs / learnOutputs / update driven
+ * sample by sample from main() (cnn.c:451-474).
+ */
+typedef struct b200cnn_layer_desc {
+    int type;                 /* B200CNN_LAYER_* */
+    int depth, width, height; /* output shape */
+    int k, pad, stride;       /* conv / pool */
+} b200cnn_layer_desc;
+enum { B200CNN_LAYER_INPUT = 0, B200CNN_LAYER_FULL = 1, B200CNN_LAYER_CONV = 2, B200CNN_LAYER_POOL = 3 };
+
+typedef struct b200cnn_engine b200cnn_engine;
+
+b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layers, int nlayers, int max_batch);
+void b200cnn_engine_destroy(b200cnn_engine* e);
+/* Dense parameter count (360,810 for the reference network) and the size in floats of the padded
+ * flat buffer the engine actually uses (every tensor starts on a 128-byte boundary). */
+size_t b200cnn_engine_num_params(const b200cnn_engine* e);
+size_t b200cnn_engine_flat_floats(const b200cnn_engine* e);
+/* offsets[2*l] / [2*l+1] = float offset of layer l's weights / biases in the flat buffer (-1 if none);
+ * sizes likewise. */
+void b200cnn_engine_param_layout(const b200cnn_engine* e, long* offsets, long* sizes);
+/* Use caller-provided device buffers (flat_floats floats each) for parameters and gradients — the
+ * data-parallel path hands in NVLink-mapped symmetric memory here.  Call before the first step. */
+int b200cnn_engine_bind_buffers(b200cnn_engine* e, float* params, float* grads);
+float* b200cnn_engine_params(b200cnn_engine* e);
+float* b200cnn_engine_grads(b200cnn_engine* e);
+/* Dense host <-> device parameter transfer (layer order, weights then biases: the CPU engine's order). */
+int b200cnn_engine_set_params(b200cnn_engine* e, const float* dense_host);
+int b200cnn_engine_get_params(b200cnn_engine* e, float* dense_host);
+int b200cnn_engine_get_grads(b200cnn_engine* e, float* dense_host);
+
+/* Forward `batch` samples.  images: uint8 [batch][c*h*w] (x_is_u8) or fp32.  With labels the loss
+ * kernel also runs (probabilities, dz of the last layer, metrics). */
+int b200cnn_engine_forward(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch,
+                           b200cnn_stream stream);
+/* Backward from the last forward: fills the gradient buffer (sum over the batch, like u_weights). */
+int b200cnn_engine_backward(b200cnn_engine* e, b200cnn_stream stream);
+/* params -= lr * grads (single GPU). */
+int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream stream);
+/* forward + backward + update in one call; lr is the per-sample-sum rate, i.e. rate / batch
+ * (cnn.c:468).  With use_graph the launch sequence is captured once per (pointers, batch) and
+ * replayed as a CUDA graph. */
+int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch,
+                              float lr, int use_graph, b200cnn_stream stream);
+/* metrics: {sum CE, sum MSE, #correct, #samples} accumulated since the last reset (device buffer). */
+float* b200cnn_engine_metrics(b200cnn_engine* e);
+int b200cnn_engine_reset_metrics(b200cnn_engine* e, b200cnn_stream stream);
+/* Copy layer l's activations of the last forward (batch * nnodes floats; last layer: probabilities). */
+int b200cnn_engine_layer_output(b200cnn_engine* e, int layer, int batch, float* host);
+/* Number of kernels one train_step launches (for launch accounting in benchmarks). */
+int b200cnn_engine_launches_per_step(const b200cnn_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

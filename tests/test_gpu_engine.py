@@ -1,0 +1,126 @@
+"""The native training engine against the PyTorch reference model and the CPU engine."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _cuda_only():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-9))
+
+
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("backend", ["simt", "auto"])
+def test_forward_backward_step_vs_torch(pool, backend):
+    from mpi_cuda_cnn_b200 import Engine, mnist_layers, pool_layers
+    from mpi_cuda_cnn_b200.models import RefCNN, dense_grads, dense_params, load_dense_params
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    F200.set_backend(backend)
+    tol = 2e-4 if backend == "simt" else 6e-3
+    B = 64
+    eng = Engine(pool_layers() if pool else mnist_layers(), max_batch=B)
+    cpu = eng.init_params(seed=0)
+    model = load_dense_params(RefCNN(pool=pool, dtype=torch.float64), cpu.get_params()).cuda()
+    x, y = F200.synthetic_batch(B, seed=11)
+    eng.reset_metrics()
+    eng.forward(x, y)
+    xr = (x.double() / 255.0).reshape(B, 1, 28, 28)
+    feats = model.features(xr)
+    L = len(eng.layers)
+    assert _rel(eng.layer_output(L - 1, B), torch.softmax(feats[-1], 1).detach().cpu().numpy()) < tol
+    assert _rel(eng.layer_output(L - 3, B), feats[2].detach().cpu().numpy()) < tol
+    m = eng.read_metrics()
+    assert m["count"] == B
+    assert m["mse_sum"] / B == pytest.approx(float(RefCNN.mse_metric(feats[-1].detach(), y)), rel=5e-3)
+    eng.backward()
+    loss = model.loss_sum(xr, y)
+    loss.backward()
+    assert m["ce_sum"] == pytest.approx(float(loss), rel=5e-3)
+    g, gr = eng.get_grads(), dense_grads(model)
+    o = 0
+    for p in model.param_list():  # per-tensor, so a small tensor cannot hide behind a big one
+        n = p.numel()
+        assert _rel(g[o:o + n], gr[o:o + n]) < tol, f"grad of tensor at offset {o}"
+        o += n
+    before = eng.get_params()
+    eng.sgd(0.1 / B)
+    torch.cuda.synchronize()
+    assert _rel(eng.get_params(), before - (0.1 / B) * g) < 1e-6
+    F200.set_backend("auto")
+    eng.close()
+
+
+def test_graph_step_equals_eager_step_and_learns():
+    from mpi_cuda_cnn_b200 import Engine
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    B = 256
+    a, b = Engine(max_batch=B), Engine(max_batch=B)
+    a.init_params(seed=0)
+    b.init_params(seed=0)
+    x, y = F200.synthetic_batch(B * 8, seed=5)
+    stream = torch.cuda.Stream()
+    xs, ys = torch.empty_like(x[:B]), torch.empty_like(y[:B])
+    first = last = None
+    with torch.cuda.stream(stream):
+        for it in range(40):
+            i = (it % 8) * B
+            xs.copy_(x[i:i + B]); ys.copy_(y[i:i + B])
+            a.reset_metrics()
+            a.train_step(xs, ys, 0.1 / B, use_graph=True)
+            b.train_step(xs, ys, 0.1 / B, use_graph=False)
+            m = a.read_metrics()
+            if it == 0:
+                first = m["mse_sum"] / B
+            last = m["mse_sum"] / B
+    torch.cuda.synchronize()
+    assert a.launches_per_step > 0
+    assert np.array_equal(a.get_params(), b.get_params())  # same kernels, same order => bitwise equal
+    assert first == pytest.approx(0.09, abs=0.02) and last < 0.5 * first  # the reference's metric falls
+    x_test, y_test = F200.synthetic_batch(B, seed=99)
+    p = a.predict(x_test)
+    acc = float((p.argmax(1) == y_test.cpu().numpy()).mean())
+    assert acc > 0.8
+    a.close(); b.close()
+
+
+def test_gpu_engine_tracks_cpu_engine():
+    """One mini-batch step on the GPU == the CPU engine (fp64) accumulating the same samples."""
+    from mpi_cuda_cnn_b200 import Engine
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    B = 16
+    eng = Engine(max_batch=B)
+    cpu = eng.init_params(seed=0)
+    x, y = F200.synthetic_batch(B, seed=21)
+    eng.train_step(x, y, 0.1 / B, use_graph=False)
+    xs, ys = x.cpu().numpy().astype(np.float64) / 255.0, y.cpu().numpy()
+    for i in range(B):
+        cpu.set_inputs(xs[i])
+        cpu.learn_outputs(np.eye(10)[ys[i]])
+    cpu.update(0.1 / B)
+    assert _rel(eng.get_params(), cpu.get_params()) < 2e-4
+    eng.close()
+
+
+def test_batch_limits_and_errors():
+    from mpi_cuda_cnn_b200 import Engine
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    eng = Engine(max_batch=8)
+    eng.init_params()
+    x, y = F200.synthetic_batch(16)
+    with pytest.raises(RuntimeError, match="batch"):
+        eng.train_step(x, y, 0.1, use_graph=False)
+    eng.close()

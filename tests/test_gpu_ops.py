@@ -1,0 +1,169 @@
+"""Every CUDA kernel against a plain PyTorch fp32 reference of the same op.
+
+Runs under both backends where the op has two implementations: 'simt' (CUDA cores, fp32 multiply) and
+'tcgen05' (tensor cores, TF32 multiply, fp32 accumulate).  Tolerances: fp32 path 2e-4 relative to the
+output scale, TF32 path 4e-3 (10-bit mantissa operands).
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"simt": 2e-4, "tcgen05": 4e-3, "auto": 4e-3}
+
+
+@pytest.fixture(autouse=True)
+def _cuda_only():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    torch.manual_seed(0)
+    yield
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    F200.set_backend("auto")
+
+
+def _close(got, want, tol):
+    scale = max(float(want.abs().max()), 1e-6)
+    err = float((got.double() - want.double()).abs().max()) / scale
+    assert err < tol, f"max rel err {err:.3e} (tol {tol})"
+
+
+def test_library_is_native_sm100a():
+    from mpi_cuda_cnn_b200 import _native as N
+
+    info = N.cuda().b200cnn_build_info().decode()
+    assert "sm_100a" in info
+    assert torch.cuda.get_device_capability()[0] == 10
+
+
+@pytest.mark.parametrize("cfg", [
+    # n, c, h, w, oc, k, pad, stride, act
+    (256, 1, 28, 28, 16, 3, 1, 2, "relu"),   # conv1 of the reference network (cnn.c:419)
+    (256, 16, 14, 14, 32, 3, 1, 2, "relu"),  # conv2 (cnn.c:422)
+    (7, 3, 11, 9, 5, 3, 0, 1, "none"),
+    (4, 16, 14, 14, 32, 3, 1, 1, "relu"),    # pooled variant
+    (3, 2, 12, 12, 20, 5, 2, 3, "tanh"),
+])
+def test_conv_forward_backward(cfg):
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    n, c, h, w, oc, k, pad, stride, act = cfg
+    x = torch.randn(n, c, h, w, device="cuda")
+    wt = (0.2 * torch.randn(oc, c, k, k, device="cuda")).requires_grad_()
+    b = (0.1 * torch.randn(oc, device="cuda")).requires_grad_()
+    torch.backends.cudnn.allow_tf32 = False
+    xr = x.clone().requires_grad_()
+    x.requires_grad_()
+    y = F200.conv2d_act(x, wt, b, stride, pad, act)
+    wr, br = wt.detach().clone().requires_grad_(), b.detach().clone().requires_grad_()
+    z = F.conv2d(xr, wr, br, stride, pad)
+    yr = {"relu": torch.relu, "tanh": torch.tanh, "none": lambda t: t}[act](z)
+    _close(y, yr, 2e-4)
+    g = torch.randn_like(yr)
+    y.backward(g)
+    yr.backward(g)
+    _close(x.grad, xr.grad, 3e-4)
+    _close(wt.grad, wr.grad, 3e-4)
+    _close(b.grad, br.grad, 3e-4)
+
+
+def test_conv_uint8_input_fuses_normalisation():
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    x8 = torch.randint(0, 256, (32, 1, 28, 28), device="cuda", dtype=torch.uint8)
+    wt = 0.2 * torch.randn(16, 1, 3, 3, device="cuda")
+    b = 0.1 * torch.randn(16, device="cuda")
+    y = F200.conv2d_act(x8, wt, b, 2, 1, "relu")
+    yr = torch.relu(F.conv2d(x8.float() / 255.0, wt, b, 2, 1))
+    _close(y, yr, 2e-4)
+
+
+@pytest.mark.parametrize("backend", ["simt", "auto"])
+@pytest.mark.parametrize("mnk", [(256, 200, 1568), (256, 200, 200), (256, 10, 200), (33, 17, 70), (1, 200, 1568), (512, 64, 96)])
+@pytest.mark.parametrize("act", ["tanh", "none"])
+def test_linear_forward_backward(backend, mnk, act):
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    F200.set_backend(backend)
+    m, n, k = mnk
+    x = torch.randn(m, k, device="cuda").requires_grad_()
+    w = (torch.randn(n, k, device="cuda") / k ** 0.5).requires_grad_()
+    b = (0.1 * torch.randn(n, device="cuda")).requires_grad_()
+    xr, wr, br = (t.detach().clone().requires_grad_() for t in (x, w, b))
+    y = F200.linear_act(x, w, b, act)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    z = F.linear(xr, wr, br)
+    yr = torch.tanh(z) if act == "tanh" else z
+    tol = TOL[backend]
+    _close(y, yr, tol)
+    g = torch.randn_like(yr)
+    y.backward(g)
+    yr.backward(g)
+    _close(x.grad, xr.grad, tol)
+    _close(w.grad, wr.grad, tol)
+    _close(b.grad, br.grad, tol)
+
+
+def test_softmax_xent_and_metrics():
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    m, n = 300, 10
+    logits = (3 * torch.randn(m, n, device="cuda")).requires_grad_()
+    labels = torch.randint(0, n, (m,), device="cuda", dtype=torch.uint8)
+    lr = logits.detach().clone().requires_grad_()
+    loss, probs, metrics = F200.softmax_xent(logits, labels)
+    want = F.cross_entropy(lr, labels.long(), reduction="sum")
+    _close(loss, want, 1e-4)
+    _close(probs, torch.softmax(lr, 1), 1e-5)
+    loss.backward()
+    want.backward()
+    _close(logits.grad, lr.grad, 1e-5)
+    p = torch.softmax(lr.detach(), 1)
+    mse = ((p - F.one_hot(labels.long(), n)) ** 2).mean(1).sum()
+    correct = (p.argmax(1) == labels.long()).sum()
+    got = metrics.cpu().numpy()
+    assert got[1] == pytest.approx(float(mse), rel=1e-4)
+    assert got[2] == float(correct) and got[3] == m
+
+
+def test_maxpool_forward_backward():
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    for (k, s, h, w) in [(2, 2, 28, 28), (3, 2, 15, 13), (3, 1, 9, 9)]:
+        x = torch.randn(5, 4, h, w, device="cuda").requires_grad_()
+        xr = x.detach().clone().requires_grad_()
+        y = F200.max_pool2d(x, k, s)
+        yr = F.max_pool2d(xr, k, s)
+        assert torch.equal(y, yr)
+        g = torch.randn_like(yr)
+        y.backward(g)
+        yr.backward(g)
+        _close(x.grad, xr.grad, 1e-6)
+
+
+def test_sgd_update():
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    w = torch.randn(360812, device="cuda")
+    g = torch.randn_like(w)
+    want = w - 0.05 * g
+    F200.sgd_update_(w, g, 0.05, zero_grad=True)
+    _close(w, want, 1e-6)
+    assert float(g.abs().max()) == 0.0
+
+
+def test_synthetic_and_gather():
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    x, y = F200.synthetic_batch(512, seed=3)
+    x2, y2 = F200.synthetic_batch(256, seed=3, first_index=256)
+    assert torch.equal(x[256:], x2) and torch.equal(y[256:], y2)  # counter-based: ranges compose
+    assert int(y.max()) < 10 and len(torch.unique(y)) == 10 and float(x.float().mean()) > 5
+    bx, by = F200.gather_batch(x, y, 64, seed=1, step=5, shard_begin=128, shard_len=128)
+    # every gathered sample is a row of the shard with its own label
+    for i in range(0, 64, 7):
+        match = (x[128:256] == bx[i]).all(1).nonzero()
+        assert match.numel() >= 1 and int(y[128 + int(match[0])]) == int(by[i])
