@@ -16,7 +16,7 @@ NVCC     := /usr/local/cuda/bin/nvcc
 # reference binary, which is built without FMA contraction.
 CXXFLAGS ?= -O3 -std=c++17 -fPIC -Wall -Wextra -ffp-contract=off
 SM_ARCH  := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS  := -O3 -std=c++17 $(SM_ARCH) -lineinfo -Xcompiler -fPIC -Xcompiler -Wall --expt-relaxed-constexpr
+NVFLAGS  := -O3 -std=c++17 $(SM_ARCH) -lineinfo -DB200CNN_HAVE_TCGEN05 -Xcompiler -fPIC -Xcompiler -Wall --expt-relaxed-constexpr
 
 PKG    := mpi_cuda_cnn_b200
 LIBDIR := $(PKG)/lib

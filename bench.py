@@ -162,7 +162,7 @@ def run_b200(args):
         m_dev = engine.read_metrics()
 
         # ---- end to end: pinned host inputs -> device, loss read back, every step -------------------
-        pool = 64
+        pool = max(1, min(64, n_data // BATCH))
         host_x = torch.empty((pool, BATCH, 784), dtype=torch.uint8).pin_memory()
         host_y = torch.empty((pool, BATCH), dtype=torch.uint8).pin_memory()
         host_x.copy_(data_x[: pool * BATCH].reshape(pool, BATCH, 784).cpu())

@@ -95,11 +95,13 @@ def test_graph_step_equals_eager_step_and_learns():
     a.close(); b.close()
 
 
-def test_gpu_engine_tracks_cpu_engine():
+@pytest.mark.parametrize("backend,tol", [("simt", 2e-4), ("auto", 5e-3)])
+def test_gpu_engine_tracks_cpu_engine(backend, tol):
     """One mini-batch step on the GPU == the CPU engine (fp64) accumulating the same samples."""
     from mpi_cuda_cnn_b200 import Engine
     from mpi_cuda_cnn_b200.ops import functional as F200
 
+    F200.set_backend(backend)
     B = 16
     eng = Engine(max_batch=B)
     cpu = eng.init_params(seed=0)
@@ -110,7 +112,8 @@ def test_gpu_engine_tracks_cpu_engine():
         cpu.set_inputs(xs[i])
         cpu.learn_outputs(np.eye(10)[ys[i]])
     cpu.update(0.1 / B)
-    assert _rel(eng.get_params(), cpu.get_params()) < 2e-4
+    assert _rel(eng.get_params(), cpu.get_params()) < tol
+    F200.set_backend("auto")
     eng.close()
 
 

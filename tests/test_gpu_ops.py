@@ -81,10 +81,11 @@ def test_conv_uint8_input_fuses_normalisation():
     _close(y, yr, 2e-4)
 
 
-@pytest.mark.parametrize("backend", ["simt", "auto"])
-@pytest.mark.parametrize("mnk", [(256, 200, 1568), (256, 200, 200), (256, 10, 200), (33, 17, 70), (1, 200, 1568), (512, 64, 96)])
-@pytest.mark.parametrize("act", ["tanh", "none"])
-def test_linear_forward_backward(backend, mnk, act):
+TC_SHAPES = [(256, 200, 1568), (256, 200, 200), (256, 16, 200), (1, 200, 1568), (512, 64, 96), (100, 36, 44), (300, 132, 260)]
+ANY_SHAPES = TC_SHAPES + [(256, 10, 200), (33, 17, 70)]
+
+
+def _linear_case(backend, mnk, act):
     from mpi_cuda_cnn_b200.ops import functional as F200
 
     F200.set_backend(backend)
@@ -105,6 +106,55 @@ def test_linear_forward_backward(backend, mnk, act):
     _close(x.grad, xr.grad, tol)
     _close(w.grad, wr.grad, tol)
     _close(b.grad, br.grad, tol)
+
+
+@pytest.mark.parametrize("mnk", ANY_SHAPES)
+@pytest.mark.parametrize("act", ["tanh", "none"])
+def test_linear_forward_backward_simt(mnk, act):
+    _linear_case("simt", mnk, act)
+
+
+@pytest.mark.parametrize("mnk", TC_SHAPES)
+@pytest.mark.parametrize("act", ["tanh", "none"])
+def test_linear_forward_backward_tcgen05(mnk, act):
+    """tcgen05 / TMEM / TMA GEMM, all three operand-major combinations (forward K/K, dX K/N, dW M/N)."""
+    _linear_case("tcgen05", mnk, act)
+
+
+def test_linear_auto_falls_back_for_unaligned_shapes():
+    _linear_case("auto", (33, 17, 70), "tanh")
+    _linear_case("auto", (256, 10, 200), "none")
+
+
+def test_tcgen05_padded_logits_layout():
+    """The engine's last layer: 10 classes in rows of 16 floats (ld = 16) through the C ABI."""
+    import ctypes as C
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    m, n, k, ld = 256, 10, 200, 16
+    x = torch.randn(m, k, device="cuda")
+    w = torch.randn(n, k, device="cuda") / k ** 0.5
+    b = torch.randn(n, device="cuda")
+    dz = torch.zeros(m, ld, device="cuda")
+    dz[:, :n] = torch.randn(m, n, device="cuda")
+    y = torch.zeros(m, ld, device="cuda")
+    dx, dw, db = torch.empty(m, k, device="cuda"), torch.empty(n, k, device="cuda"), torch.empty(n, device="cuda")
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    N.check(lib.b200cnn_set_backend(N.BACKEND_TCGEN05))
+    try:
+        N.check(lib.b200cnn_linear_fwd(p(x), p(w), p(b), p(y), m, n, k, ld, N.ACT_NONE, st), "fwd")
+        N.check(lib.b200cnn_linear_bwd_data(p(dz), p(w), p(x), N.ACT_TANH, p(dx), m, n, k, ld, st), "bwd_data")
+        N.check(lib.b200cnn_linear_bwd_weight(p(dz), p(x), p(dw), p(db), 0, m, n, k, ld, st), "bwd_weight")
+    finally:
+        lib.b200cnn_set_backend(N.BACKEND_AUTO)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    _close(y[:, :n], x @ w.T + b, 4e-3)
+    assert float(y[:, n:].abs().max()) == 0.0
+    _close(dx, (dz[:, :n] @ w) * (1 - x * x), 4e-3)
+    _close(dw, dz[:, :n].T @ x, 4e-3)
+    _close(db, dz[:, :n].sum(0), 1e-4)
 
 
 def test_softmax_xent_and_metrics():
