@@ -40,3 +40,16 @@ extern "C" int b200cnn_linear_bwd_weight(const float* dz, const float* x, float*
     if (g_backend == B200CNN_BACKEND_TCGEN05) return set_error(kInvalidValue, "linear_bwd_weight: shape not supported by the tcgen05 path");
     return simt_linear_bwd_weight(dz, x, dw, db, accumulate, m, n, k, lddz, as_stream(stream));
 }
+
+// ---- NHWC tensor-core convolution entry points (see include/b200cnn.h) ------------------------------
+extern "C" int b200cnn_conv3x3_fwd_nhwc(const float* x_nhwc, const float* w, const float* b, float* y, int ldy,
+                                        const b200cnn_conv_shape* s, int act, b200cnn_stream stream) {
+    if (!s || !tc_conv3x3_fwd_supported(s)) return set_error(kInvalidValue, "conv3x3_fwd_nhwc: shape not supported by the tcgen05 path");
+    return tc_conv3x3_fwd(x_nhwc, w, b, y, ldy, s, act, as_stream(stream));
+}
+
+extern "C" int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev,
+                                               float* dx_nhwc, const b200cnn_conv_shape* s, b200cnn_stream stream) {
+    if (!s || !tc_conv3x3s2_bwd_data_supported(s)) return set_error(kInvalidValue, "conv3x3s2_bwd_data_nhwc: shape not supported by the tcgen05 path");
+    return tc_conv3x3s2_bwd_data(dz_nhwc, w, a_prev_nhwc, act_prev, dx_nhwc, s, as_stream(stream));
+}

@@ -1,0 +1,345 @@
+// 3x3 convolution on the tensor cores as an IMPLICIT GEMM fed by TMA — no im2col matrix exists in
+// memory.  Activations between the convolutions are NHWC (channels innermost), so for one filter tap
+// (ky,kx) the GEMM operand "all output pixels x input channels" is a strided 4-D box of the input:
+//     dims (C, W, H, N), box (C, (OW-1)*s+1, (OH-1)*s+1, G) walked with traversal strides (1, s, s, 1)
+// started at (0, kx-pad, ky-pad, n0).  TMA delivers it as [G*OH*OW rows][C floats] with out-of-bounds
+// (padding) elements zero-filled, already in the swizzled K-major layout tcgen05.mma reads.  A 3x3
+// convolution is then 9 taps x (C/8) MMAs accumulating into one TMEM tile.
+//
+//   forward        y[n][oc][oy][ox] = relu(b + sum_tap sum_c x[n][oy*s-p+ky][ox*s-p+kx][c] w[oc][c][ky][kx])
+//                  A = input taps (TMA, K-major SW64), B = weights (gathered from OIHW into SW64 tiles),
+//                  epilogue: bias + ReLU, stored CHW-flattened [n][oc*OH*OW + p] — the layout the
+//                  reference's first FC layer indexes (/root/reference/cnn.c:116-121 over :179-206).
+//   backward-data  dx[n][y][x][c] = relu'(a_prev) * sum_tap sum_oc dz[n][oy][ox][oc] w[oc][c][ky][kx]
+//                  (stride 2: the four (y%2, x%2) parity classes are four small dense GEMMs over
+//                  shifted views of dz; 4 TMA tiles, 9 tap-MMAs, 4 accumulators in TMEM.)
+//
+// Replaces Layer_feedForw_conv / the data half of Layer_feedBack_conv (cnn.c:175-247) and the
+// reference's only kernel, conv_forward_kernel (CUDAcnn.cu:167-195: scalar fp64, batch 1, no ReLU).
+#include "backend.cuh"
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace b200cnn {
+
+namespace {
+
+using namespace tc;
+
+constexpr int kConvThreads = 192;  // warp 0: TMA, warp 1: TMEM + MMA, warps 2-5: weights gather + epilogue
+constexpr int kTaps = 9;
+constexpr int kCin = 16;           // input channels of the forward kernel: one 64-byte swizzle row per pixel
+constexpr int kTileRows = 128;     // UMMA M
+
+struct ConvFwdArgs {
+    const float* w;     // OIHW
+    const float* bias;  // [oc]
+    float* y;           // [n][ldy], CHW-flattened per sample
+    int ldy;
+    int n, oc, oh, ow, pad, group;  // group = samples per CTA
+    int act;
+};
+
+// ---- forward -------------------------------------------------------------------------------------
+template <int OC>
+__global__ void __launch_bounds__(kConvThreads, 1)
+tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a) {
+    constexpr int kATile = kTileRows * kCin * 4;  // 8 KiB per tap (rows beyond group*oh*ow stay unused)
+    constexpr int kBTile = OC * kCin * 4;         // OC rows x 64 B per tap
+    constexpr int kTmemCols = OC < 32 ? 32 : OC;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* a_tiles = smem;
+    uint8_t* b_tiles = smem + kTaps * kATile;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + kTaps * kBTile);
+    uint64_t* tmem_full_bar = full_bar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+    const int n0 = blockIdx.x * a.group;
+    const int pix = a.oh * a.ow;
+    const int rows = min(a.group, a.n - n0) * pix;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_x);
+        mbar_init(full_bar, 1);
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // One barrier for the whole K extent: 9 tap boxes of group*oh*ow pixels x 64 B.
+            mbar_arrive_expect_tx(full_bar, uint32_t(kTaps * a.group * pix * kCin * 4));
+#pragma unroll
+            for (int t = 0; t < kTaps; t++)
+                tma_load_4d(a_tiles + t * kATile, &tmap_x, full_bar, 0, t % 3 - a.pad, t / 3 - a.pad, n0);
+        }
+    } else if (warp >= 2) {
+        // Weights: OIHW -> per-tap K-major [oc][c] tiles in the 64-byte-swizzle layout
+        // (16-byte chunk index ^= (row >> 1) & 3, cute Swizzle<2,4,3>).
+        for (int i = threadIdx.x - 64; i < OC * kCin * kTaps; i += kConvThreads - 64) {
+            const int t = i % kTaps, c = (i / kTaps) % kCin, oc = i / (kTaps * kCin);  // i walks OIHW linearly
+            const int chunk = (c >> 2) ^ ((oc >> 1) & 3);
+            *reinterpret_cast<float*>(b_tiles + t * kBTile + oc * 64 + chunk * 16 + (c & 3) * 4) = __ldg(a.w + i);
+        }
+        fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor-core (async) proxy
+    }
+    __syncthreads();
+
+    if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_tf32(kTileRows, OC, false, false);
+            mbar_wait(full_bar, 0);
+            tcgen05_fence_after();
+            const uint32_t a_addr = smem_u32(a_tiles), b_addr = smem_u32(b_tiles);
+#pragma unroll
+            for (int t = 0; t < kTaps; t++)
+#pragma unroll
+                for (int kk = 0; kk < kCin / 8; kk++) {
+                    const uint64_t da = make_smem_desc(a_addr + t * kATile + kk * 32, 16, 512, kSw64);
+                    const uint64_t db = make_smem_desc(b_addr + t * kBTile + kk * 32, 16, 512, kSw64);
+                    umma_tf32(tmem_base, da, db, idesc, (t | kk) != 0);
+                }
+            umma_commit(tmem_full_bar);
+        }
+    } else if (warp >= 2) {
+        const int q = warp & 3;
+        const int r = 32 * q + lane;
+        mbar_wait(tmem_full_bar, 0);
+        tcgen05_fence_after();
+        const bool live = r < rows;
+        const int g = r / pix, p = r % pix;
+        float* out = a.y + size_t(n0 + g) * a.ldy + p;
+#pragma unroll 1
+        for (int c0 = 0; c0 < OC; c0 += 16) {
+            float v[16];
+            __syncwarp();
+            tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(c0), v);
+            if (live) {
+#pragma unroll
+                for (int i = 0; i < 16; i++)
+                    out[size_t(c0 + i) * pix] = apply_act(a.act, v[i] + __ldg(a.bias + c0 + i));
+            }
+        }
+        __syncwarp();
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
+// ---- backward-data (3x3, stride 2, pad 1) ------------------------------------------------------------
+struct ConvBwdArgs {
+    const float* w;       // OIHW [oc][c][3][3]
+    const float* a_prev;  // NHWC [n][h][w][c] activation that fed the conv (ReLU mask), or NULL
+    float* dx;            // NHWC [n][h][w][c]
+    int n, oh, ow, h, w_in, group;
+    int act_prev;
+};
+
+// Output-gradient channels OC = 32 (one 128-byte swizzle row per pixel), input channels C = 16.
+template <int OC, int C>
+__global__ void __launch_bounds__(kConvThreads, 1)
+tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBwdArgs a) {
+    static_assert(OC == 32, "one 128-byte row of dz per output pixel");
+    constexpr int kATile = kTileRows * OC * 4;  // 16 KiB per shift (dj, di)
+    constexpr int kBTile = C * OC * 4;          // [c rows][oc] per tap, 128-byte rows
+    constexpr int kTmemCols = 64 < 4 * C ? 4 * C : 64;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* a_tiles = smem;                  // 4 shifted views of dz
+    uint8_t* b_tiles = smem + 4 * kATile;     // 9 taps
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + kTaps * kBTile);
+    uint64_t* tmem_full_bar = full_bar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+    const int n0 = blockIdx.x * a.group;
+    const int pix = a.oh * a.ow;
+    const int rows = min(a.group, a.n - n0) * pix;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_dz);
+        mbar_init(full_bar, 1);
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(full_bar, uint32_t(4 * a.group * pix * OC * 4));
+#pragma unroll
+            for (int sft = 0; sft < 4; sft++)  // shift (dj, di): rows (j, i) read dz[n][j+dj][i+di][:], zero past the edge
+                tma_load_4d(a_tiles + sft * kATile, &tmap_dz, full_bar, 0, sft & 1, sft >> 1, n0);
+        }
+    } else if (warp >= 2) {
+        // Weights per tap as the B operand [n = c][k = oc], K-major 128-byte rows, 128B swizzle
+        // (16-byte chunk ^= row & 7).
+        for (int i = threadIdx.x - 64; i < OC * C * kTaps; i += kConvThreads - 64) {
+            const int t = i % kTaps, c = (i / kTaps) % C, oc = i / (kTaps * C);
+            const int chunk = (oc >> 2) ^ (c & 7);
+            *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = __ldg(a.w + i);
+        }
+        fence_proxy_async_smem();
+    }
+    __syncthreads();
+
+    if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_tf32(kTileRows, C, false, false);
+            mbar_wait(full_bar, 0);
+            tcgen05_fence_after();
+            const uint32_t a_addr = smem_u32(a_tiles), b_addr = smem_u32(b_tiles);
+            // Input pixel (2j+py, 2i+px) receives tap (ky,kx) from output pixel (j+dj, i+di):
+            //   py = 0: ky = 1, dj = 0          py = 1: ky = 0, dj = 1  and  ky = 2, dj = 0     (same for x)
+#pragma unroll
+            for (int cls = 0; cls < 4; cls++) {
+                const int py = cls >> 1, px = cls & 1;
+                bool first = true;
+#pragma unroll
+                for (int ky = 0; ky < 3; ky++) {
+                    if ((py == 0) != (ky == 1)) continue;
+                    const int dj = (ky == 0) ? 1 : 0;
+#pragma unroll
+                    for (int kx = 0; kx < 3; kx++) {
+                        if ((px == 0) != (kx == 1)) continue;
+                        const int di = (kx == 0) ? 1 : 0;
+                        const int sft = dj * 2 + di, t = ky * 3 + kx;
+#pragma unroll
+                        for (int kk = 0; kk < OC / 8; kk++) {
+                            const uint64_t da = make_smem_desc(a_addr + sft * kATile + kk * 32, 16, 1024, kSw128);
+                            const uint64_t db = make_smem_desc(b_addr + t * kBTile + kk * 32, 16, 1024, kSw128);
+                            umma_tf32(tmem_base + cls * C, da, db, idesc, !(first && kk == 0));
+                        }
+                        first = false;
+                    }
+                }
+            }
+            umma_commit(tmem_full_bar);
+        }
+    } else if (warp >= 2) {
+        const int q = warp & 3;
+        const int r = 32 * q + lane;
+        mbar_wait(tmem_full_bar, 0);
+        tcgen05_fence_after();
+        const bool live = r < rows;
+        const int g = r / pix, p = r % pix, j = p / a.ow, i = p % a.ow;
+#pragma unroll 1
+        for (int cls = 0; cls < 4; cls++) {
+            float v[16];
+            __syncwarp();
+            tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(cls * C), v);
+            const int y = 2 * j + (cls >> 1), x = 2 * i + (cls & 1);
+            if (live && y < a.h && x < a.w_in) {
+                const size_t off = ((size_t(n0 + g) * a.h + y) * a.w_in + x) * C;
+                if (a.a_prev) {
+                    const float4* ap = reinterpret_cast<const float4*>(a.a_prev + off);
+#pragma unroll
+                    for (int k4 = 0; k4 < C / 4; k4++) {
+                        const float4 av = __ldg(ap + k4);
+                        v[4 * k4 + 0] *= act_grad_from_output(a.act_prev, av.x);
+                        v[4 * k4 + 1] *= act_grad_from_output(a.act_prev, av.y);
+                        v[4 * k4 + 2] *= act_grad_from_output(a.act_prev, av.z);
+                        v[4 * k4 + 3] *= act_grad_from_output(a.act_prev, av.w);
+                    }
+                }
+                float4* dp = reinterpret_cast<float4*>(a.dx + off);
+#pragma unroll
+                for (int k4 = 0; k4 < C / 4; k4++) dp[k4] = make_float4(v[4 * k4], v[4 * k4 + 1], v[4 * k4 + 2], v[4 * k4 + 3]);
+            }
+        }
+        __syncwarp();
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
+}  // namespace
+
+bool tc_conv3x3_fwd_supported(const b200cnn_conv_shape* s) {
+    return s->k == 3 && s->c == kCin && (s->oc == 16 || s->oc == 32 || s->oc == 64) && s->oh * s->ow <= kTileRows &&
+           s->stride >= 1 && s->stride <= 8 && (s->ow - 1) * s->stride + 1 <= 256 && (s->oh - 1) * s->stride + 1 <= 256;
+}
+
+// x: NHWC [n][h][w][16]; y: [n][ldy] with the sample's outputs CHW-flattened (ldy >= oc*oh*ow).
+int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s,
+                   int act, cudaStream_t st) {
+    if (!tc_conv3x3_fwd_supported(s)) return set_error(kInvalidValue, "tc_conv3x3_fwd: unsupported shape");
+    const int pix = s->oh * s->ow;
+    const int group = kTileRows / pix;
+    CUtensorMap tm;
+    const uint64_t dims[4] = {uint64_t(s->c), uint64_t(s->w), uint64_t(s->h), uint64_t(s->n)};
+    const uint64_t strides[4] = {0, uint64_t(s->c) * 4, uint64_t(s->w) * s->c * 4, uint64_t(s->h) * s->w * s->c * 4};
+    const uint32_t box[4] = {uint32_t(s->c), uint32_t((s->ow - 1) * s->stride + 1), uint32_t((s->oh - 1) * s->stride + 1),
+                             uint32_t(group)};
+    const uint32_t estr[4] = {1, uint32_t(s->stride), uint32_t(s->stride), 1};
+    if (int rc = encode_tmap_f32(&tm, x_nhwc, 4, dims, strides, box, estr, 64)) return rc;
+    ConvFwdArgs a{w, b, y, ldy, s->n, s->oc, s->oh, s->ow, s->pad, group, act};
+    const int grid = ceil_div(s->n, group);
+#define B200CNN_LAUNCH_FWD(OCV)                                                                                   \
+    do {                                                                                                          \
+        auto kern = tc_conv3x3_fwd_kernel<OCV>;                                                                   \
+        constexpr size_t smem = size_t(kTaps) * (kTileRows * kCin * 4 + OCV * kCin * 4) + 1024 + 64;               \
+        static bool configured = false;                                                                           \
+        if (!configured) {                                                                                        \
+            B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));      \
+            configured = true;                                                                                    \
+        }                                                                                                         \
+        kern<<<grid, kConvThreads, smem, st>>>(tm, a);                                                            \
+    } while (0)
+    if (s->oc == 16) B200CNN_LAUNCH_FWD(16);
+    else if (s->oc == 32) B200CNN_LAUNCH_FWD(32);
+    else B200CNN_LAUNCH_FWD(64);
+#undef B200CNN_LAUNCH_FWD
+    B200CNN_CHECK_LAUNCH("tc_conv3x3_fwd");
+    return 0;
+}
+
+bool tc_conv3x3s2_bwd_data_supported(const b200cnn_conv_shape* s) {
+    return s->k == 3 && s->stride == 2 && s->pad == 1 && s->c == 16 && s->oc == 32 && s->oh * s->ow <= kTileRows &&
+           s->h == 2 * s->oh && s->w == 2 * s->ow;
+}
+
+// dz: NHWC [n][oh][ow][32]; a_prev / dx: NHWC [n][h][w][16].
+int tc_conv3x3s2_bwd_data(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
+                          const b200cnn_conv_shape* s, cudaStream_t st) {
+    if (!tc_conv3x3s2_bwd_data_supported(s)) return set_error(kInvalidValue, "tc_conv3x3s2_bwd_data: unsupported shape");
+    const int pix = s->oh * s->ow;
+    const int group = kTileRows / pix;
+    CUtensorMap tm;
+    const uint64_t dims[4] = {uint64_t(s->oc), uint64_t(s->ow), uint64_t(s->oh), uint64_t(s->n)};
+    const uint64_t strides[4] = {0, uint64_t(s->oc) * 4, uint64_t(s->ow) * s->oc * 4, uint64_t(pix) * s->oc * 4};
+    const uint32_t box[4] = {uint32_t(s->oc), uint32_t(s->ow), uint32_t(s->oh), uint32_t(group)};
+    if (int rc = encode_tmap_f32(&tm, dz_nhwc, 4, dims, strides, box, nullptr, 128)) return rc;
+    ConvBwdArgs a{w, a_prev_nhwc, dx_nhwc, s->n, s->oh, s->ow, s->h, s->w, group, act_prev};
+    auto kern = tc_conv3x3s2_bwd_data_kernel<32, 16>;
+    constexpr size_t smem = 4 * size_t(kTileRows) * 32 * 4 + kTaps * 16 * 32 * 4 + 1024 + 64;
+    static bool configured = false;
+    if (!configured) {
+        B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        configured = true;
+    }
+    kern<<<ceil_div(s->n, group), kConvThreads, smem, st>>>(tm, a);
+    B200CNN_CHECK_LAUNCH("tc_conv3x3s2_bwd_data");
+    return 0;
+}
+
+}  // namespace b200cnn

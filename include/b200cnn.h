@@ -62,6 +62,15 @@ size_t b200cnn_conv2d_bwd_weight_scratch_bytes(const b200cnn_conv_shape* s);
 int b200cnn_conv2d_bwd_weight(const float* dz, const void* x, int x_is_u8, float* dw, float* db, int accumulate,
                               void* scratch, const b200cnn_conv_shape* s, b200cnn_stream stream);
 
+/* Tensor-core (tcgen05) implicit-GEMM convolutions on NHWC activations: the engine's fast path for
+ * 3x3 convolutions whose input has 16 channels.  x / dz / dx / a_prev are NHWC; the forward output is
+ * written per sample CHW-flattened with row stride ldy (what the next FC layer reads, cnn.c:116-121). */
+int b200cnn_conv3x3_fwd_nhwc(const float* x_nhwc, const float* w, const float* b, float* y, int ldy,
+                             const b200cnn_conv_shape* s, int act, b200cnn_stream stream);
+/* 3x3 / stride 2 / pad 1, 32 -> 16 channels: dx = conv_transpose(dz, w) * act'(a_prev). */
+int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev,
+                                    float* dx_nhwc, const b200cnn_conv_shape* s, b200cnn_stream stream);
+
 /* ---- fully connected (K4, K6) ------------------------------------------------------------- */
 /* y[m][n] = act(sum_k x[m][k] w[n][k] + b[n]); ldy = row stride of y in floats (>= n).
  * Replaces Layer_feedForw_full (cnn.c:113-150). */

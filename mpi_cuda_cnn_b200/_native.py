@@ -123,6 +123,8 @@ def cuda():
     _sig(lib, "b200cnn_conv2d_bwd_data", i, vp, vp, vp, i, vp, cs, vp)
     _sig(lib, "b200cnn_conv2d_bwd_weight_scratch_bytes", sz, cs)
     _sig(lib, "b200cnn_conv2d_bwd_weight", i, vp, vp, i, vp, vp, i, vp, cs, vp)
+    _sig(lib, "b200cnn_conv3x3_fwd_nhwc", i, vp, vp, vp, vp, i, cs, i, vp)
+    _sig(lib, "b200cnn_conv3x3s2_bwd_data_nhwc", i, vp, vp, vp, i, vp, cs, vp)
     _sig(lib, "b200cnn_linear_fwd", i, vp, vp, vp, vp, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_linear_bwd_data", i, vp, vp, vp, i, vp, i, i, i, i, vp)
     _sig(lib, "b200cnn_linear_bwd_weight", i, vp, vp, vp, vp, i, i, i, i, i, vp)
