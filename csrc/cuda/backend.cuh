@@ -24,6 +24,13 @@ int tc_linear_fwd(const float* x, const float* w, const float* b, float* y, int 
                   cudaStream_t st);
 int tc_linear_bwd_data(const float* dz, const float* w, const float* a_prev, int act_prev, float* dx, int m, int n,
                        int k, int lddz, cudaStream_t st);
+// Last layer fused with the loss: probs = softmax(x W^T + b), dz = probs - onehot, metrics (n <= 16 classes).
+bool tc_linear_softmax_supported(int m, int n, int k, int ld);
+int tc_linear_softmax_xent(const float* x, const float* w, const float* b, const uint8_t* labels, float* probs, float* dz,
+                           float* metrics, int m, int n, int k, int ld, cudaStream_t st);
+// Same as tc_linear_bwd_data but column n of dx is stored at (n % perm_p) * perm_c + n / perm_p.
+int tc_linear_bwd_data_permuted(const float* dz, const float* w, const float* a_prev, int act_prev, float* dx, int m, int n,
+                                int k, int lddz, int perm_p, int perm_c, cudaStream_t st);
 int tc_linear_bwd_weight(const float* dz, const float* x, float* dw, float* db, int accumulate, int m, int n, int k,
                          int lddz, cudaStream_t st);
 
@@ -32,10 +39,18 @@ bool tc_conv3x3_fwd_supported(const b200cnn_conv_shape* s);
 int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s,
                    int act, cudaStream_t st);
 bool tc_conv3x3s2_bwd_data_supported(const b200cnn_conv_shape* s);
-int tc_conv3x3s2_bwd_data(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
-                          const b200cnn_conv_shape* s, cudaStream_t st);
+int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
+                          float* dx_nhwc, const b200cnn_conv_shape* s, cudaStream_t st);
 
-// conv.cu
+// conv_nhwc.cu / conv.cu
+bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
+int nhwc_bwd_weight_chunks(int n, int* spb_out);
+int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
+                         float* partials, const b200cnn_conv_shape* s, cudaStream_t st);
+int simt_conv2d_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* y, const b200cnn_conv_shape* s,
+                    int act, int nhwc_out, cudaStream_t st);
+int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks, int nw, int nb, int accumulate,
+                         cudaStream_t st);
 int launch_conv2d_bwd_weight(const float* dz, const void* x, int x_is_u8, float* dw, float* db, int accumulate,
                              float* partials, const b200cnn_conv_shape* s, cudaStream_t st);
 

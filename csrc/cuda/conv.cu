@@ -33,7 +33,7 @@ __device__ __forceinline__ float load_in<uint8_t>(const uint8_t* p, size_t i, fl
 template <typename TIn>
 __global__ void __launch_bounds__(kConvThreads)
 conv2d_fwd_kernel(const TIn* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-                  float* __restrict__ y, b200cnn_conv_shape s, int act, float in_scale) {
+                  float* __restrict__ y, b200cnn_conv_shape s, int act, float in_scale, int nhwc_out) {
     extern __shared__ __align__(16) float ws[];
     const int ckk = s.c * s.k * s.k;
     const int oc0 = blockIdx.y * kOcTile;
@@ -74,9 +74,21 @@ conv2d_fwd_kernel(const TIn* __restrict__ x, const float* __restrict__ w, const 
         }
     }
     const size_t opix = size_t(oy) * s.ow + ox, oplane = size_t(s.oh) * s.ow;
+    if (nhwc_out && oc0 + kOcTile <= s.oc && (s.oc & 3) == 0) {
+        // channels innermost: this thread's 16 channels are 64 contiguous bytes
+        float4* dst = reinterpret_cast<float4*>(y + (size_t(n) * oplane + opix) * s.oc + oc0);
 #pragma unroll
-    for (int o = 0; o < kOcTile; o++)
-        if (oc0 + o < s.oc) y[(size_t(n) * s.oc + oc0 + o) * oplane + opix] = apply_act(act, acc[o]);
+        for (int q = 0; q < kOcTile / 4; q++)
+            dst[q] = make_float4(apply_act(act, acc[4 * q]), apply_act(act, acc[4 * q + 1]), apply_act(act, acc[4 * q + 2]),
+                                 apply_act(act, acc[4 * q + 3]));
+        return;
+    }
+#pragma unroll
+    for (int o = 0; o < kOcTile; o++) {
+        if (oc0 + o >= s.oc) continue;
+        const size_t idx = nhwc_out ? (size_t(n) * oplane + opix) * s.oc + oc0 + o : (size_t(n) * s.oc + oc0 + o) * oplane + opix;
+        y[idx] = apply_act(act, acc[o]);
+    }
 }
 
 // One thread = one input pixel (n, y, x) x kIcTile input channels; gathers from the <= ceil(k/stride)^2
@@ -197,14 +209,37 @@ conv2d_bwd_weight_partial_kernel(const float* __restrict__ dz, const TIn* __rest
 
 // Backward-weight, pass 2: sum the per-block partials in block order (fixed order => bitwise
 // reproducible), write / accumulate into dw and db.
-__global__ void conv2d_bwd_weight_reduce_kernel(const float* __restrict__ partials, float* __restrict__ dw,
-                                                float* __restrict__ db, int nchunks, int nw, int nb,
-                                                int accumulate) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+// Block = 32 outputs x 8 chunk-slices: every thread sums its slice of the chunks with all loads in
+// flight, then the 8 slice sums are added in slice order through shared memory.  The summation tree is
+// fixed, so the result is bitwise reproducible.
+constexpr int kRedSlices = 8;
+__global__ void __launch_bounds__(32 * kRedSlices)
+conv2d_bwd_weight_reduce_kernel(const float* __restrict__ partials, float* __restrict__ dw, float* __restrict__ db,
+                                int nchunks, int nw, int nb, int accumulate) {
+    __shared__ float red[kRedSlices][32];
+    const int lane = threadIdx.x % 32, slice = threadIdx.x / 32;
+    const int j = blockIdx.x * 32 + lane;
     const int nout = nw + nb;
-    if (j >= nout) return;
     float a = 0.0f;
-    for (int c = 0; c < nchunks; c++) a += __ldg(partials + size_t(c) * nout + j);
+    if (j < nout) {
+        int c = slice;
+        for (; c + 3 * kRedSlices < nchunks; c += 4 * kRedSlices) {
+            const float v0 = __ldg(partials + size_t(c) * nout + j);
+            const float v1 = __ldg(partials + size_t(c + kRedSlices) * nout + j);
+            const float v2 = __ldg(partials + size_t(c + 2 * kRedSlices) * nout + j);
+            const float v3 = __ldg(partials + size_t(c + 3 * kRedSlices) * nout + j);
+            a += v0;
+            a += v1;
+            a += v2;
+            a += v3;
+        }
+        for (; c < nchunks; c += kRedSlices) a += __ldg(partials + size_t(c) * nout + j);
+    }
+    red[slice][lane] = a;
+    __syncthreads();
+    if (slice != 0 || j >= nout) return;
+#pragma unroll
+    for (int sl = 1; sl < kRedSlices; sl++) a += red[sl][lane];
     if (j < nw ? dw == nullptr : db == nullptr) return;
     float* dst = j < nw ? dw + j : db + (j - nw);
     *dst = accumulate ? *dst + a : a;
@@ -230,18 +265,34 @@ bool shape_ok(const b200cnn_conv_shape* s) {
 
 using namespace b200cnn;
 
+namespace b200cnn {
+int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks, int nw, int nb, int accumulate,
+                         cudaStream_t st) {
+    conv2d_bwd_weight_reduce_kernel<<<ceil_div(nw + nb, 32), 32 * kRedSlices, 0, st>>>(partials, dw, db, chunks, nw, nb, accumulate);
+    B200CNN_CHECK_LAUNCH("conv2d_bwd_weight(reduce)");
+    return 0;
+}
+int simt_conv2d_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* y, const b200cnn_conv_shape* s,
+                    int act, int nhwc_out, cudaStream_t st);
+}  // namespace b200cnn
+
 extern "C" int b200cnn_conv2d_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* y,
                                   const b200cnn_conv_shape* s, int act, b200cnn_stream stream) {
+    return simt_conv2d_fwd(x, x_is_u8, w, b, y, s, act, 0, as_stream(stream));
+}
+
+int b200cnn::simt_conv2d_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* y,
+                             const b200cnn_conv_shape* s, int act, int nhwc_out, cudaStream_t stream) {
     if (!shape_ok(s)) return set_error(kInvalidValue, "conv2d_fwd: inconsistent shape");
     const size_t smem = size_t(s->c) * s->k * s->k * kOcTile * sizeof(float);
     if (smem > 48 * 1024) return set_error(kInvalidValue, "conv2d_fwd: c*k*k = %d too large for the direct kernel", s->c * s->k * s->k);
     const dim3 grid(ceil_div(s->n * s->oh * s->ow, kConvThreads), ceil_div(s->oc, kOcTile));
     if (x_is_u8)
-        conv2d_fwd_kernel<uint8_t><<<grid, kConvThreads, smem, as_stream(stream)>>>(
-            static_cast<const uint8_t*>(x), w, b, y, *s, act, 1.0f / 255.0f);
+        conv2d_fwd_kernel<uint8_t><<<grid, kConvThreads, smem, stream>>>(static_cast<const uint8_t*>(x), w, b, y, *s, act,
+                                                                         1.0f / 255.0f, nhwc_out);
     else
-        conv2d_fwd_kernel<float><<<grid, kConvThreads, smem, as_stream(stream)>>>(static_cast<const float*>(x), w, b,
-                                                                                 y, *s, act, 1.0f);
+        conv2d_fwd_kernel<float><<<grid, kConvThreads, smem, stream>>>(static_cast<const float*>(x), w, b, y, *s, act, 1.0f,
+                                                                       nhwc_out);
     B200CNN_CHECK_LAUNCH("conv2d_fwd");
     return 0;
 }
@@ -295,10 +346,7 @@ int launch_conv2d_bwd_weight(const float* dz, const void* x, int x_is_u8, float*
 #undef DISPATCH_R
 #undef LAUNCH_BW
     B200CNN_CHECK_LAUNCH("conv2d_bwd_weight(partial)");
-    conv2d_bwd_weight_reduce_kernel<<<ceil_div(nout, 256), 256, 0, st>>>(partials, dw, db, chunks, nw, s->oc,
-                                                                         accumulate);
-    B200CNN_CHECK_LAUNCH("conv2d_bwd_weight(reduce)");
-    return 0;
+    return reduce_conv_partials(partials, dw, db, chunks, nw, s->oc, accumulate, st);
 }
 }  // namespace b200cnn
 

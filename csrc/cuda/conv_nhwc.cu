@@ -1,0 +1,220 @@
+// CUDA-core kernels of the NHWC convolution chain that do not map onto tcgen05 with TF32 operands:
+//   * backward-weight: the GEMM is dW[oc][c,tap] = sum_pixels dz[pixel][oc] * patch[pixel][c,tap], i.e. both
+//     operands are "pixel-major".  TF32 M/N-major UMMA operands exist only in the 128B/32B-atom layout,
+//     which needs 32 contiguous floats per pixel per operand; a 16-channel tap slice has 16.  So these
+//     stay register-tiled FMA kernels (4 oc x 4 c per thread, float4 shared-memory reads), ~58 MFLOP.
+//   * the first convolution's backward-weight (1 input channel, 144 weights).
+// Both write per-block partial sums that conv2d_bwd_weight_reduce sums in a fixed order.
+// Replaces the weight half of Layer_feedBack_conv (/root/reference/cnn.c:236, :242).
+#include "backend.cuh"
+#include "common.cuh"
+
+namespace b200cnn {
+namespace {
+
+template <typename TIn>
+__device__ __forceinline__ float cvt_in(TIn v, float scale);
+template <>
+__device__ __forceinline__ float cvt_in<float>(float v, float) { return v; }
+template <>
+__device__ __forceinline__ float cvt_in<uint8_t>(uint8_t v, float scale) { return float(v) * scale; }
+
+// Valid output range [lo, hi) along one axis for filter offset k: 0 <= o*stride - pad + k < in.
+__device__ __forceinline__ void tap_range(int k, int stride, int pad, int in, int out, int& lo, int& hi) {
+    lo = max(0, (pad - k + stride - 1) / stride);
+    hi = min(out, (in - 1 + pad - k) / stride + 1);
+}
+
+// x NHWC [n][h][w][C], dz NHWC or CHW [n][..] (dz_chw); thread = (4 oc, 4 c, 1 tap).  All `spb` samples of the
+// block are staged in shared memory in ONE load phase (the kernel is latency-, not throughput-bound).
+__global__ void __launch_bounds__(512)
+conv_bwd_weight_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ dz, float* __restrict__ partials,
+                            b200cnn_conv_shape s, int spb, int dz_chw) {
+    extern __shared__ __align__(16) float sm[];
+    const int C = s.c, OC = s.oc, kk = s.k * s.k;
+    const int pix = s.oh * s.ow;
+    const int in_sz = s.h * s.w * C, out_sz = pix * OC;
+    const int c4n = C / 4, oc4n = OC / 4;
+    const int t = threadIdx.x;
+    const int nthr_work = oc4n * c4n * kk;
+    const bool worker = t < nthr_work;
+    const int oc4 = t % oc4n, c4 = (t / oc4n) % c4n, tap = t / (oc4n * c4n);
+    const int ky = tap / s.k, kx = tap % s.k;
+    const bool bias_thread = worker && tap == 0 && c4 == 0;
+
+    const int n0 = blockIdx.x * spb, ns = min(spb, s.n - n0);
+    float* xs = sm;                       // [ns][h][w][C]
+    float* gs = sm + size_t(spb) * in_sz; // [ns][pix][OC]
+    {
+        const float4* xg = reinterpret_cast<const float4*>(x + size_t(n0) * in_sz);
+        for (int i = t; i < ns * in_sz / 4; i += blockDim.x) reinterpret_cast<float4*>(xs)[i] = __ldg(xg + i);
+        if (!dz_chw) {
+            const float4* gg = reinterpret_cast<const float4*>(dz + size_t(n0) * out_sz);
+            for (int i = t; i < ns * out_sz / 4; i += blockDim.x) reinterpret_cast<float4*>(gs)[i] = __ldg(gg + i);
+        } else {
+            // CHW -> HWC while staging: coalesced reads along the pixel index.
+            for (int i = t; i < ns * out_sz; i += blockDim.x) {
+                const int p = i % pix, oc = (i / pix) % OC, nn = i / out_sz;
+                gs[(nn * pix + p) * OC + oc] = __ldg(dz + size_t(n0) * out_sz + i);
+            }
+        }
+    }
+    __syncthreads();
+    if (!worker) return;
+
+    float acc[4][4];
+    float bacc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+    int oy0, oy1, ox0, ox1;
+    tap_range(ky, s.stride, s.pad, s.h, s.oh, oy0, oy1);
+    tap_range(kx, s.stride, s.pad, s.w, s.ow, ox0, ox1);
+
+    for (int nn = 0; nn < ns; nn++) {
+        const float* xsn = xs + nn * in_sz;
+        const float* gsn = gs + nn * out_sz;
+        if (bias_thread)
+            for (int p = 0; p < pix; p++) {
+                const float4 g = *reinterpret_cast<const float4*>(gsn + p * OC + oc4 * 4);
+                bacc[0] += g.x; bacc[1] += g.y; bacc[2] += g.z; bacc[3] += g.w;
+            }
+        for (int oy = oy0; oy < oy1; oy++) {
+            const float* xrow = xsn + ((oy * s.stride - s.pad + ky) * s.w - s.pad + kx) * C + c4 * 4;
+            const float* grow = gsn + oy * s.ow * OC + oc4 * 4;
+#pragma unroll 4
+            for (int ox = ox0; ox < ox1; ox++) {
+                const float4 g = *reinterpret_cast<const float4*>(grow + ox * OC);
+                const float4 a = *reinterpret_cast<const float4*>(xrow + ox * s.stride * C);
+                acc[0][0] = fmaf(g.x, a.x, acc[0][0]); acc[0][1] = fmaf(g.x, a.y, acc[0][1]);
+                acc[0][2] = fmaf(g.x, a.z, acc[0][2]); acc[0][3] = fmaf(g.x, a.w, acc[0][3]);
+                acc[1][0] = fmaf(g.y, a.x, acc[1][0]); acc[1][1] = fmaf(g.y, a.y, acc[1][1]);
+                acc[1][2] = fmaf(g.y, a.z, acc[1][2]); acc[1][3] = fmaf(g.y, a.w, acc[1][3]);
+                acc[2][0] = fmaf(g.z, a.x, acc[2][0]); acc[2][1] = fmaf(g.z, a.y, acc[2][1]);
+                acc[2][2] = fmaf(g.z, a.z, acc[2][2]); acc[2][3] = fmaf(g.z, a.w, acc[2][3]);
+                acc[3][0] = fmaf(g.w, a.x, acc[3][0]); acc[3][1] = fmaf(g.w, a.y, acc[3][1]);
+                acc[3][2] = fmaf(g.w, a.z, acc[3][2]); acc[3][3] = fmaf(g.w, a.w, acc[3][3]);
+            }
+        }
+    }
+    const int nw = OC * C * kk, nout = nw + OC;
+    float* out = partials + size_t(blockIdx.x) * nout;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) out[((oc4 * 4 + i) * C + c4 * 4 + j) * kk + tap] = acc[i][j];  // OIHW
+    if (bias_thread)
+#pragma unroll
+        for (int i = 0; i < 4; i++) out[nw + oc4 * 4 + i] = bacc[i];
+}
+
+// Single input channel: x [n][h][w] (uint8 or float), dz NHWC [n][oh][ow][OC].
+// thread = (oc, tap, pixel-row slice): kSlices threads share one output and are summed through shared memory.
+constexpr int kC1Slices = 4;
+
+template <typename TIn>
+__global__ void __launch_bounds__(1024)
+conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restrict__ dz, float* __restrict__ partials,
+                               b200cnn_conv_shape s, int spb, float in_scale) {
+    extern __shared__ __align__(16) float sm[];
+    const int OC = s.oc, kk = s.k * s.k, pix = s.oh * s.ow;
+    const int in_sz = s.h * s.w, in_pad = (in_sz + 3) & ~3, out_sz = pix * OC;
+    const int t = threadIdx.x;
+    const int nw = OC * kk, nout = nw + OC;
+    const int n0 = blockIdx.x * spb, ns = min(spb, s.n - n0);
+    float* xs = sm;                         // [ns][in_pad]
+    float* gs = sm + size_t(spb) * in_pad;  // [ns][pix][OC]
+    float* red = gs + size_t(spb) * out_sz; // [kC1Slices][nout]
+    for (int i = t; i < ns * in_sz; i += blockDim.x)
+        xs[(i / in_sz) * in_pad + i % in_sz] = cvt_in<TIn>(__ldg(x + size_t(n0) * in_sz + i), in_scale);
+    {
+        const float4* gg = reinterpret_cast<const float4*>(dz + size_t(n0) * out_sz);
+        for (int i = t; i < ns * out_sz / 4; i += blockDim.x) reinterpret_cast<float4*>(gs)[i] = __ldg(gg + i);
+    }
+    __syncthreads();
+    const int o = t % nout, slice = t / nout;  // blockDim = nout * kC1Slices (rounded up to a warp)
+    if (slice < kC1Slices) {
+        float acc = 0.f;
+        if (o < nw) {
+            const int oc = o % OC, tap = o / OC;
+            const int ky = tap / s.k, kx = tap % s.k;
+            int oy0, oy1, ox0, ox1;
+            tap_range(ky, s.stride, s.pad, s.h, s.oh, oy0, oy1);
+            tap_range(kx, s.stride, s.pad, s.w, s.ow, ox0, ox1);
+            for (int nn = 0; nn < ns; nn++)
+                for (int oy = oy0 + slice; oy < oy1; oy += kC1Slices) {
+                    const float* xrow = xs + nn * in_pad + (oy * s.stride - s.pad + ky) * s.w - s.pad + kx;
+                    const float* grow = gs + (nn * pix + oy * s.ow) * OC + oc;
+#pragma unroll 7
+                    for (int ox = ox0; ox < ox1; ox++) acc = fmaf(grow[ox * OC], xrow[ox * s.stride], acc);
+                }
+        } else {
+            for (int nn = 0; nn < ns; nn++)
+                for (int p = slice; p < pix; p += kC1Slices) acc += gs[(nn * pix + p) * OC + (o - nw)];
+        }
+        red[slice * nout + o] = acc;
+    }
+    __syncthreads();
+    if (t < nout) {
+        float a = red[t];
+#pragma unroll
+        for (int sl = 1; sl < kC1Slices; sl++) a += red[sl * nout + t];
+        // OIHW with one input channel: index oc*kk + tap; bias after the weights.
+        const int oc = t % OC, tap = t / OC;
+        partials[size_t(blockIdx.x) * nout + (t < nw ? oc * kk + tap : t)] = a;
+    }
+}
+
+}  // namespace
+
+int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks, int nw, int nb, int accumulate,
+                         cudaStream_t st);
+
+bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8) {
+    if (s->c == 1) return s->oc * s->k * s->k + s->oc <= 512 && s->oc % 4 == 0;
+    return !x_is_u8 && s->c % 4 == 0 && s->oc % 4 == 0 && (s->oc / 4) * (s->c / 4) * s->k * s->k <= 512;
+}
+
+// Blocks (= partial sums) used for a batch of n samples.
+int nhwc_bwd_weight_chunks(int n, int* spb_out) {
+    int spb = ceil_div(n, 148);
+    if (spb < 1) spb = 1;
+    if (spb_out) *spb_out = spb;
+    return ceil_div(n, spb);
+}
+
+// x: NHWC float (or [n][h][w] uint8/float when c == 1); dz: NHWC, or CHW when dz_chw (c > 1 only).
+// dw OIHW, db [oc].  partials: chunks*(nw+oc) floats.
+int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
+                         float* partials, const b200cnn_conv_shape* s, cudaStream_t st) {
+    if (!nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: unsupported shape");
+    int spb = 1;
+    const int chunks = nhwc_bwd_weight_chunks(s->n, &spb);
+    const int kk = s->k * s->k, nw = s->oc * s->c * kk;
+    if (s->c == 1) {
+        if (dz_chw) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: CHW gradients are only read by the multi-channel kernel");
+        const int nout = nw + s->oc;
+        const int threads = ((nout * kC1Slices + 31) / 32) * 32;
+        const size_t smem = (size_t(spb) * (((s->h * s->w + 3) & ~3) + size_t(s->oh) * s->ow * s->oc) + size_t(kC1Slices) * nout) * sizeof(float);
+        if (threads > 1024 || smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: layer too large for the single-channel kernel");
+        if (x_is_u8) {
+            if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+            conv_bwd_weight_c1_nhwc_kernel<uint8_t><<<chunks, threads, smem, st>>>(static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f);
+        } else {
+            if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+            conv_bwd_weight_c1_nhwc_kernel<float><<<chunks, threads, smem, st>>>(static_cast<const float*>(x), dz, partials, *s, spb, 1.0f);
+        }
+    } else {
+        const int work = (s->oc / 4) * (s->c / 4) * kk;
+        const int threads = ((work + 31) / 32) * 32;
+        const size_t smem = size_t(spb) * (size_t(s->h) * s->w * s->c + size_t(s->oh) * s->ow * s->oc) * sizeof(float);
+        if (smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: samples do not fit shared memory");
+        if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_nhwc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        conv_bwd_weight_nhwc_kernel<<<chunks, threads, smem, st>>>(static_cast<const float*>(x), dz, partials, *s, spb, dz_chw);
+    }
+    B200CNN_CHECK_LAUNCH("nhwc_conv_bwd_weight");
+    return reduce_conv_partials(partials, dw, db, chunks, nw, s->oc, accumulate, st);
+}
+
+}  // namespace b200cnn

@@ -63,6 +63,11 @@ struct b200cnn_engine {
     cudaStream_t g_stream = nullptr;
     b200cnn_comm* comm = nullptr;
     int launches_per_step = 0;
+    cudaStream_t side = nullptr;          // weight-gradient kernels run here, next to the data-gradient chain
+    cudaEvent_t ev_dz = nullptr, ev_data = nullptr, ev_side = nullptr;
+    bool last_fast = false;   // layout of layer 1's activations in the last forward (NHWC when true)
+    bool fast_chain = false;  // conv(C_in=1) -> tc conv3x3 -> FC pattern: NHWC activations + tcgen05 convolutions
+    int g_backend = -1;
 };
 
 namespace {
@@ -85,9 +90,15 @@ b200cnn_conv_shape conv_shape(const EngineLayer& prev, const EngineLayer& l, int
     return s;
 }
 
+// The tensor-core convolution chain is used when the topology allows it and the backend is not pinned
+// to the CUDA-core kernels.
+bool use_fast_chain(const b200cnn_engine* e) { return e->fast_chain && current_backend() != B200CNN_BACKEND_SIMT; }
+
 int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
                     cudaStream_t st, int* launches) {
     auto& L = e->layers;
+    const bool fast = use_fast_chain(e);
+    e->last_fast = fast;
     for (size_t li = 1; li < L.size(); li++) {
         EngineLayer& l = L[li];
         const EngineLayer& p = L[li - 1];
@@ -97,7 +108,13 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
         switch (l.d.type) {
             case B200CNN_LAYER_CONV: {
                 const b200cnn_conv_shape s = conv_shape(p, l, batch);
-                rc = b200cnn_conv2d_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, l.a, &s, l.act, st);
+                if (fast && li == 1)  // first conv: CUDA cores (1 input channel), NHWC output for the TMA loads below
+                    rc = simt_conv2d_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, l.a, &s, l.act, 1, st);
+                else if (fast && li == 2)  // implicit GEMM on tcgen05, output CHW-flattened for the FC layer
+                    rc = tc_conv3x3_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a, l.ld, &s,
+                                        l.act, st);
+                else
+                    rc = b200cnn_conv2d_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, l.a, &s, l.act, st);
                 break;
             }
             case B200CNN_LAYER_POOL:
@@ -107,6 +124,14 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
                 break;
             case B200CNN_LAYER_FULL:
                 if (in_u8) return set_error(kInvalidValue, "engine: a full layer cannot read uint8 input directly");
+                if (li + 1 == L.size()) {  // output layer: GEMM + softmax + loss gradient + metrics
+                    rc = b200cnn_linear_softmax_xent(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off,
+                                                     labels, l.a, labels ? l.dz : nullptr, labels ? e->metrics : nullptr,
+                                                     batch, l.nnodes, p.nnodes, l.ld, st);
+                    if (!rc && launches)
+                        (*launches) += (current_backend() != B200CNN_BACKEND_SIMT && tc_linear_softmax_supported(batch, l.nnodes, p.nnodes, l.ld)) ? 0 : 1;
+                    break;
+                }
                 rc = b200cnn_linear_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a,
                                         batch, l.nnodes, p.nnodes, l.ld, l.act, st);
                 break;
@@ -115,12 +140,6 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
         if (rc) return rc;
         if (launches) (*launches)++;
     }
-    // Softmax over the last layer's logits, in place; with labels also dz and the metrics.
-    EngineLayer& out = L.back();
-    const int rc = b200cnn_softmax_xent(out.a, labels, out.a, labels ? out.dz : nullptr, labels ? e->metrics : nullptr,
-                                        batch, out.nnodes, out.ld, st);
-    if (rc) return rc;
-    if (launches) (*launches)++;
     return 0;
 }
 
@@ -136,55 +155,79 @@ int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, cudaStream_t st, 
     return 0;
 }
 
+// Backward.  The data-gradient chain (dz of layer l -> dz of layer l-1) is the critical path and stays on
+// `st`; every weight-gradient kernel only needs its own layer's dz, so it runs on the engine's side
+// stream, concurrently with the rest of the chain.  (Inside a captured step these become parallel
+// branches of the CUDA graph.)  Order on the side stream per layer:
+//     wait(dz ready) -> dW/db kernel(s) -> wait(this layer's data gradient issued) -> fused update hook
+// The hook must come after the data-gradient kernel because a two-shot / NVLS update may overwrite the
+// layer's weights on this GPU from a peer.
 int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch, cudaStream_t st, int* launches) {
     auto& L = e->layers;
     float* grads = cur_grads(e);
+    const bool fast = use_fast_chain(e);
+    cudaStream_t side = e->side;
     for (size_t li = L.size() - 1; li >= 1; li--) {
         EngineLayer& l = L[li];
         EngineLayer& p = L[li - 1];
         const void* in = (li == 1) ? images : static_cast<const void*>(p.a);
         const int in_u8 = (li == 1) ? is_u8 : 0;
         int rc = 0;
-        switch (l.d.type) {
-            case B200CNN_LAYER_FULL:
-                // Data gradient first: once the layer's update is launched (two-shot / NVLS variants) a
-                // peer may overwrite this layer's weights, so nothing may read them afterwards.
-                if (li > 1) {
-                    rc = b200cnn_linear_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, batch, l.nnodes,
-                                                 p.nnodes, l.ld, st);
-                    if (rc) return rc;
-                    if (launches) (*launches)++;
-                }
-                rc = b200cnn_linear_bwd_weight(l.dz, static_cast<const float*>(in), grads + l.w_off, grads + l.b_off,
-                                               0, batch, l.nnodes, p.nnodes, l.ld, st);
+        if (l.d.type == B200CNN_LAYER_POOL) {
+            if (li > 1) {
+                rc = b200cnn_maxpool_bwd(l.dz, l.argmax, p.a, p.act, p.dz, batch, p.d.depth, p.d.height, p.d.width, l.d.k,
+                                         l.d.stride, st);
                 if (rc) return rc;
                 if (launches) (*launches)++;
-                if ((rc = layer_grads_ready(e, l, st, launches))) return rc;
-                break;
-            case B200CNN_LAYER_CONV: {
-                const b200cnn_conv_shape s = conv_shape(p, l, batch);
-                if (li > 1) {
-                    rc = b200cnn_conv2d_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, &s, st);
-                    if (rc) return rc;
-                    if (launches) (*launches)++;
-                }
-                rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0, e->scratch, &s, st);
-                if (rc) return rc;
-                if (launches) (*launches) += 2;
-                if ((rc = layer_grads_ready(e, l, st, launches))) return rc;
-                break;
             }
-            case B200CNN_LAYER_POOL:
-                if (li > 1) {
-                    rc = b200cnn_maxpool_bwd(l.dz, l.argmax, p.a, p.act, p.dz, batch, p.d.depth, p.d.height, p.d.width,
-                                             l.d.k, l.d.stride, st);
-                    if (rc) return rc;
-                    if (launches) (*launches)++;
-                }
-                break;
-            default: return set_error(kInvalidValue, "engine: bad layer type %d", l.d.type);
+            continue;
+        }
+        if (l.d.type != B200CNN_LAYER_FULL && l.d.type != B200CNN_LAYER_CONV)
+            return set_error(kInvalidValue, "engine: bad layer type %d", l.d.type);
+
+        // l.dz is complete on `st` here: fork the weight-gradient work.
+        B200CNN_CUDA(cudaEventRecord(e->ev_dz, st));
+        B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_dz, 0));
+        if (l.d.type == B200CNN_LAYER_FULL) {
+            rc = b200cnn_linear_bwd_weight(l.dz, static_cast<const float*>(in), grads + l.w_off, grads + l.b_off, 0, batch,
+                                           l.nnodes, p.nnodes, l.ld, side);
+            if (launches) (*launches)++;
+        } else {
+            const b200cnn_conv_shape s = conv_shape(p, l, batch);
+            if (fast && li <= 2)
+                rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/li == 2, grads + l.w_off, grads + l.b_off, 0, e->scratch,
+                                          &s, side);
+            else
+                rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0, e->scratch, &s, side);
+            if (launches) (*launches) += 2;
+        }
+        if (rc) return rc;
+
+        // Data gradient for the layer below (critical path).
+        if (li > 1) {
+            if (l.d.type == B200CNN_LAYER_FULL) {
+                rc = b200cnn_linear_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, batch, l.nnodes, p.nnodes, l.ld, st);
+            } else {
+                const b200cnn_conv_shape s = conv_shape(p, l, batch);
+                if (fast && li == 2)
+                    rc = tc_conv3x3s2_bwd_data(l.dz, /*dz_is_chw=*/1, e->params + l.w_off, p.a, p.act, p.dz, &s, st);
+                else
+                    rc = b200cnn_conv2d_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, &s, st);
+            }
+            if (rc) return rc;
+            if (launches) (*launches)++;
+        }
+        if (e->comm) {
+            if (li > 1) {
+                B200CNN_CUDA(cudaEventRecord(e->ev_data, st));
+                B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_data, 0));
+            }
+            if ((rc = layer_grads_ready(e, l, side, launches))) return rc;
         }
     }
+    // Join: everything on the side stream is ordered before whatever follows on `st`.
+    B200CNN_CUDA(cudaEventRecord(e->ev_side, side));
+    B200CNN_CUDA(cudaStreamWaitEvent(st, e->ev_side, 0));
     return 0;
 }
 
@@ -271,6 +314,19 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
         e->layers.push_back(l);
     }
     e->flat_floats = off;
+    if (nlayers >= 4 && e->layers[1].d.type == B200CNN_LAYER_CONV && e->layers[0].d.depth == 1 &&
+        e->layers[2].d.type == B200CNN_LAYER_CONV && e->layers[3].d.type == B200CNN_LAYER_FULL) {
+        const b200cnn_conv_shape s1 = conv_shape(e->layers[0], e->layers[1], max_batch);
+        const b200cnn_conv_shape s2 = conv_shape(e->layers[1], e->layers[2], max_batch);
+        e->fast_chain = tc_conv3x3_fwd_supported(&s2) && tc_conv3x3s2_bwd_data_supported(&s2) &&
+                        nhwc_bwd_weight_supported(&s1, 1) && nhwc_bwd_weight_supported(&s2, 0) && s1.oc % 16 == 0 &&
+                        tc_linear_bwd_data_supported(max_batch, e->layers[3].nnodes, e->layers[2].nnodes, e->layers[3].ld);
+        if (e->fast_chain) {
+            const size_t chunks = size_t(nhwc_bwd_weight_chunks(max_batch, nullptr));
+            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[2].nw + e->layers[2].nb) * sizeof(float));
+            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float));
+        }
+    }
     e->scratch_bytes = round_up(scratch_bytes, 512);
     const size_t arena_bytes = arena_floats * sizeof(float) + e->scratch_bytes + 1024;
     if (cudaMalloc(&e->arena, arena_bytes) != cudaSuccess || cudaMemset(e->arena, 0, arena_bytes) != cudaSuccess) {
@@ -289,6 +345,15 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
             cur += round_up(size_t(max_batch) * l.nnodes, kAlignFloats);
         }
     }
+    if (cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ev_dz, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ev_data, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ev_side, cudaEventDisableTiming) != cudaSuccess) {
+        set_error(int(cudaGetLastError()), "engine_create: cannot create the side stream");
+        cudaFree(e->arena);
+        delete e;
+        return nullptr;
+    }
     e->scratch = cur;
     cur += e->scratch_bytes / sizeof(float);
     e->metrics = cur;
@@ -304,6 +369,10 @@ extern "C" void b200cnn_engine_destroy(b200cnn_engine* e) {
         cudaFree(e->params);
         cudaFree(e->grads);
     }
+    if (e->ev_dz) cudaEventDestroy(e->ev_dz);
+    if (e->ev_data) cudaEventDestroy(e->ev_data);
+    if (e->ev_side) cudaEventDestroy(e->ev_side);
+    if (e->side) cudaStreamDestroy(e->side);
     cudaFree(e->arena);
     delete e;
 }
@@ -433,7 +502,7 @@ extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, 
         return rc;
     }
     const bool same_key = e->g_images == images && e->g_labels == labels && e->g_batch == batch &&
-                          e->g_is_u8 == x_is_u8 && e->g_stream == st;
+                          e->g_is_u8 == x_is_u8 && e->g_stream == st && e->g_backend == current_backend();
     if (!same_key) {
         for (cudaGraphExec_t& g : e->graph_exec)
             if (g) {
@@ -461,6 +530,7 @@ extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, 
         e->g_batch = batch;
         e->g_is_u8 = x_is_u8;
         e->g_stream = st;
+        e->g_backend = current_backend();
         e->launches_per_step = launches;
     }
     B200CNN_CUDA(cudaGraphLaunch(e->graph_exec[par], st));
@@ -480,6 +550,17 @@ extern "C" int b200cnn_engine_layer_output(b200cnn_engine* e, int layer, int bat
     const EngineLayer& l = e->layers[size_t(layer)];
     B200CNN_CUDA(cudaMemcpy2D(host, l.nnodes * sizeof(float), l.a, l.ld * sizeof(float), l.nnodes * sizeof(float),
                               size_t(batch), cudaMemcpyDeviceToHost));
+    if (e->last_fast && layer == 1) {
+        // The tensor-core chain keeps this layer NHWC on the device; callers always get CHW.
+        const int c = l.d.depth, hw = l.d.width * l.d.height;
+        std::vector<float> tmp(size_t(l.nnodes));
+        for (int b = 0; b < batch; b++) {
+            float* row = host + size_t(b) * l.nnodes;
+            std::memcpy(tmp.data(), row, tmp.size() * sizeof(float));
+            for (int p = 0; p < hw; p++)
+                for (int ch = 0; ch < c; ch++) row[size_t(ch) * hw + p] = tmp[size_t(p) * c + ch];
+        }
+    }
     return 0;
 }
 

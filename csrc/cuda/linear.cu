@@ -41,6 +41,15 @@ extern "C" int b200cnn_linear_bwd_weight(const float* dz, const float* x, float*
     return simt_linear_bwd_weight(dz, x, dw, db, accumulate, m, n, k, lddz, as_stream(stream));
 }
 
+extern "C" int b200cnn_linear_softmax_xent(const float* x, const float* w, const float* b, const uint8_t* labels, float* probs,
+                                           float* dz, float* metrics, int m, int n, int k, int ld, b200cnn_stream stream) {
+    if (g_backend != B200CNN_BACKEND_SIMT && tc_linear_softmax_supported(m, n, k, ld))
+        return tc_linear_softmax_xent(x, w, b, labels, probs, dz, metrics, m, n, k, ld, as_stream(stream));
+    if (g_backend == B200CNN_BACKEND_TCGEN05) return set_error(kInvalidValue, "linear_softmax_xent: shape not supported by the tcgen05 path");
+    if (int rc = simt_linear_fwd(x, w, b, probs, m, n, k, ld, B200CNN_ACT_NONE, as_stream(stream))) return rc;
+    return b200cnn_softmax_xent(probs, labels, probs, labels ? dz : nullptr, labels ? metrics : nullptr, m, n, ld, stream);
+}
+
 // ---- NHWC tensor-core convolution entry points (see include/b200cnn.h) ------------------------------
 extern "C" int b200cnn_conv3x3_fwd_nhwc(const float* x_nhwc, const float* w, const float* b, float* y, int ldy,
                                         const b200cnn_conv_shape* s, int act, b200cnn_stream stream) {
@@ -48,8 +57,21 @@ extern "C" int b200cnn_conv3x3_fwd_nhwc(const float* x_nhwc, const float* w, con
     return tc_conv3x3_fwd(x_nhwc, w, b, y, ldy, s, act, as_stream(stream));
 }
 
-extern "C" int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev,
-                                               float* dx_nhwc, const b200cnn_conv_shape* s, b200cnn_stream stream) {
+extern "C" int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc,
+                                               int act_prev, float* dx_nhwc, const b200cnn_conv_shape* s,
+                                               b200cnn_stream stream) {
     if (!s || !tc_conv3x3s2_bwd_data_supported(s)) return set_error(kInvalidValue, "conv3x3s2_bwd_data_nhwc: shape not supported by the tcgen05 path");
-    return tc_conv3x3s2_bwd_data(dz_nhwc, w, a_prev_nhwc, act_prev, dx_nhwc, s, as_stream(stream));
+    return tc_conv3x3s2_bwd_data(dz, dz_is_chw, w, a_prev_nhwc, act_prev, dx_nhwc, s, as_stream(stream));
+}
+
+// dw (OIHW) / db of a convolution whose input x is NHWC (or a 1-channel image, uint8 allowed) and whose
+// output gradient is NHWC (or CHW when dz_is_chw).  scratch as for b200cnn_conv2d_bwd_weight.
+extern "C" int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const float* dz, int dz_is_chw, float* dw, float* db,
+                                              int accumulate, void* scratch, const b200cnn_conv_shape* s,
+                                              b200cnn_stream stream) {
+    if (!s || !scratch || !nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "conv2d_bwd_weight_nhwc: unsupported shape or missing scratch");
+    return nhwc_conv_bwd_weight(x, x_is_u8, dz, dz_is_chw, dw, db, accumulate, static_cast<float*>(scratch), s, as_stream(stream));
+}
+extern "C" size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s) {
+    return size_t(nhwc_bwd_weight_chunks(s->n, nullptr)) * (size_t(s->oc) * s->c * s->k * s->k + s->oc) * sizeof(float);
 }

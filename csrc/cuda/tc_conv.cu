@@ -139,6 +139,7 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a)
 
 // ---- backward-data (3x3, stride 2, pad 1) ------------------------------------------------------------
 struct ConvBwdArgs {
+    const float* dz_chw;  // if non-NULL: dz as [n][oc][oh][ow] (what the FC layer above produces); gathered by threads
     const float* w;       // OIHW [oc][c][3][3]
     const float* a_prev;  // NHWC [n][h][w][c] activation that fed the conv (ReLU mask), or NULL
     float* dx;            // NHWC [n][h][w][c]
@@ -179,14 +180,32 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
+    if (a.dz_chw) {
+        // dz arrives CHW (the FC layer's gradient w.r.t. its flattened input): transpose it on the fly into
+        // the four shifted K-major tiles, 128-byte rows, 128B swizzle.  Reads are coalesced along the pixel
+        // index; each thread writes one 16-byte chunk (4 channels of one pixel), conflict-free thanks to
+        // the swizzle.
+        for (int i = threadIdx.x; i < 4 * (OC / 4) * kTileRows; i += kConvThreads) {
+            const int r = i % kTileRows, oc4 = (i / kTileRows) % (OC / 4), sft = i / (kTileRows * (OC / 4));
+            if (r >= rows) continue;
+            const int g = r / pix, p = r % pix;
+            const int jj = p / a.ow + (sft >> 1), ix = p % a.ow + (sft & 1);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (jj < a.oh && ix < a.ow) {
+                const float* src = a.dz_chw + (size_t(n0 + g) * OC + oc4 * 4) * pix + jj * a.ow + ix;
+                v = make_float4(__ldg(src), __ldg(src + pix), __ldg(src + 2 * pix), __ldg(src + 3 * pix));
+            }
+            *reinterpret_cast<float4*>(a_tiles + sft * kATile + r * 128 + ((oc4 ^ (r & 7)) << 4)) = v;
+        }
+    } else if (warp == 0) {
         if (lane == 0) {
             mbar_arrive_expect_tx(full_bar, uint32_t(4 * a.group * pix * OC * 4));
 #pragma unroll
             for (int sft = 0; sft < 4; sft++)  // shift (dj, di): rows (j, i) read dz[n][j+dj][i+di][:], zero past the edge
                 tma_load_4d(a_tiles + sft * kATile, &tmap_dz, full_bar, 0, sft & 1, sft >> 1, n0);
         }
-    } else if (warp >= 2) {
+    }
+    if (warp >= 2) {
         // Weights per tap as the B operand [n = c][k = oc], K-major 128-byte rows, 128B swizzle
         // (16-byte chunk ^= row & 7).
         for (int i = threadIdx.x - 64; i < OC * C * kTaps; i += kConvThreads - 64) {
@@ -194,14 +213,14 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
             const int chunk = (oc >> 2) ^ (c & 7);
             *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = __ldg(a.w + i);
         }
-        fence_proxy_async_smem();
     }
+    fence_proxy_async_smem();
     __syncthreads();
 
     if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc_tf32(kTileRows, C, false, false);
-            mbar_wait(full_bar, 0);
+            if (!a.dz_chw) mbar_wait(full_bar, 0);
             tcgen05_fence_after();
             const uint32_t a_addr = smem_u32(a_tiles), b_addr = smem_u32(b_tiles);
             // Input pixel (2j+py, 2i+px) receives tap (ky,kx) from output pixel (j+dj, i+di):
@@ -318,9 +337,10 @@ bool tc_conv3x3s2_bwd_data_supported(const b200cnn_conv_shape* s) {
            s->h == 2 * s->oh && s->w == 2 * s->ow;
 }
 
-// dz: NHWC [n][oh][ow][32]; a_prev / dx: NHWC [n][h][w][16].
-int tc_conv3x3s2_bwd_data(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
-                          const b200cnn_conv_shape* s, cudaStream_t st) {
+// dz: NHWC [n][oh][ow][32], or CHW [n][32][oh][ow] when dz_is_chw; a_prev / dx: NHWC [n][h][w][16].
+int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
+                          float* dx_nhwc, const b200cnn_conv_shape* s, cudaStream_t st) {
+    const float* dz_nhwc = dz;
     if (!tc_conv3x3s2_bwd_data_supported(s)) return set_error(kInvalidValue, "tc_conv3x3s2_bwd_data: unsupported shape");
     const int pix = s->oh * s->ow;
     const int group = kTileRows / pix;
@@ -329,7 +349,7 @@ int tc_conv3x3s2_bwd_data(const float* dz_nhwc, const float* w, const float* a_p
     const uint64_t strides[4] = {0, uint64_t(s->oc) * 4, uint64_t(s->ow) * s->oc * 4, uint64_t(pix) * s->oc * 4};
     const uint32_t box[4] = {uint32_t(s->oc), uint32_t(s->ow), uint32_t(s->oh), uint32_t(group)};
     if (int rc = encode_tmap_f32(&tm, dz_nhwc, 4, dims, strides, box, nullptr, 128)) return rc;
-    ConvBwdArgs a{w, a_prev_nhwc, dx_nhwc, s->n, s->oh, s->ow, s->h, s->w, group, act_prev};
+    ConvBwdArgs a{dz_is_chw ? dz : nullptr, w, a_prev_nhwc, dx_nhwc, s->n, s->oh, s->ow, s->h, s->w, group, act_prev};
     auto kern = tc_conv3x3s2_bwd_data_kernel<32, 16>;
     constexpr size_t smem = 4 * size_t(kTileRows) * 32 * 4 + kTaps * 16 * 32 * 4 + 1024 + 64;
     static bool configured = false;

@@ -62,11 +62,14 @@ using namespace tc;
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 32;   // floats: one 128-byte swizzle row
 constexpr int UMMA_K = 8;     // TF32: 32 bytes of K per instruction
-constexpr int kStages = 4;
+// Deeper rings for narrower tiles: at these sizes a CTA is bound by the latency of its own operand stream,
+// so the ring is sized to keep ~150-190 KiB of TMA loads in flight.
+template <int BLOCK_N>
+constexpr int stages_for() { return BLOCK_N <= 16 ? 10 : BLOCK_N <= 32 ? 9 : BLOCK_N <= 64 ? 7 : 5; }
 constexpr int kThreads = 192;
 constexpr int kABytes = BLOCK_M * BLOCK_K * 4;  // 16 KiB per stage, either major
 
-enum Epi { kEpiBiasAct = 0, kEpiActGrad = 1, kEpiStore = 2 };
+enum Epi { kEpiBiasAct = 0, kEpiActGrad = 1, kEpiStore = 2, kEpiSoftmax = 3 };
 
 struct EpiArgs {
     float* C;
@@ -77,11 +80,17 @@ struct EpiArgs {
     int act;
     float* rowsum;      // [M]  (+)= sum_k A(m,k) (kEpiStore, A M-major)
     int accumulate;
+    // kEpiSoftmax (N <= 16): C = probabilities, dz = probs - onehot(labels), metrics[4] += {CE, MSE, #correct, #rows}
+    const uint8_t* labels;
+    float* dz;
+    float* metrics;
+    int perm_p, perm_c; // kEpiActGrad: if perm_p > 0 store column n at (n % perm_p) * perm_c + n / perm_p
+                        // (CHW-flattened -> HWC: hands the convolution below its NHWC gradient directly)
 };
 
 template <int BLOCK_N>
 constexpr size_t smem_bytes() {
-    return size_t(kStages) * (kABytes + BLOCK_N * BLOCK_K * 4) + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    return size_t(stages_for<BLOCK_N>()) * (kABytes + BLOCK_N * BLOCK_K * 4) + 1024 /*alignment slack*/ + 512 /*barriers*/;
 }
 
 template <int BLOCK_N, bool A_MN, bool B_MN, int EPI>
@@ -90,6 +99,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                int N, int K) {
     static_assert(BLOCK_N % 16 == 0 && BLOCK_N >= 16 && BLOCK_N <= 256, "UMMA N for M=128");
     static_assert(!B_MN || BLOCK_N % 32 == 0, "an N-major B tile is made of 32-float column groups");
+    constexpr int kStages = stages_for<BLOCK_N>();
     constexpr int kBBytes = BLOCK_N * BLOCK_K * 4;
     constexpr int kStageBytes = kABytes + kBBytes;
     constexpr int kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;  // power of two >= 32 (BLOCK_N is 16/32/64/128)
@@ -199,6 +209,63 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
+        if (EPI == kEpiSoftmax) {
+            // Whole row (<= 16 logits) in this thread: softmax, cross-entropy gradient and the reference's
+            // metrics (cnn.c:125-143, :275-286, :508-513) without another kernel or another pass over memory.
+            float v[16];
+            tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16), v);
+            float ce = 0.f, mse = 0.f, correct = 0.f, count = 0.f;
+            if (m < M) {
+                float mx = -3.0e38f;
+                int arg = 0;
+#pragma unroll
+                for (int i = 0; i < 16; i++)
+                    if (i < N) {
+                        v[i] += ep.bias ? __ldg(ep.bias + i) : 0.0f;
+                        if (mx < v[i]) {
+                            mx = v[i];
+                            arg = i;
+                        }
+                    }
+                float sum = 0.f;
+#pragma unroll
+                for (int i = 0; i < 16; i++)
+                    if (i < N) {
+                        v[i] = __expf(v[i] - mx);
+                        sum += v[i];
+                    }
+                const float inv = 1.0f / sum;
+                const int label = ep.labels ? int(ep.labels[m]) : -1;
+                float* prow = ep.C + size_t(m) * ep.ldc;
+                float* drow = ep.dz ? ep.dz + size_t(m) * ep.ldc : nullptr;
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    const float pr = i < N ? v[i] * inv : 0.0f;
+                    const float e = i < N ? pr - (i == label ? 1.0f : 0.0f) : 0.0f;
+                    if (i < ep.ldc) {
+                        prow[i] = pr;
+                        if (drow) drow[i] = e;
+                    }
+                    mse += e * e;
+                    if (i == label) ce = -__logf(fmaxf(pr, 1e-30f));
+                }
+                mse /= N;
+                correct = (arg == label) ? 1.0f : 0.0f;
+                count = 1.0f;
+            }
+            if (ep.metrics && ep.labels) {
+                ce = warp_sum(ce);
+                mse = warp_sum(mse);
+                correct = warp_sum(correct);
+                count = warp_sum(count);
+                if (lane == 0 && count > 0.f) {
+                    atomicAdd(ep.metrics + 0, ce);
+                    atomicAdd(ep.metrics + 1, mse);
+                    atomicAdd(ep.metrics + 2, correct);
+                    atomicAdd(ep.metrics + 3, count);
+                }
+            }
+        } else
 #pragma unroll 1
         for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
             float v[16];
@@ -224,7 +291,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     for (int i = 0; i < 16; i++)
                         if (i < valid) v[i] += crow[i];
                 }
-                if (valid == 16 && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
+                if (EPI == kEpiActGrad && ep.perm_p > 0) {
+                    float* orow = ep.C + size_t(m) * ep.ldc;
+#pragma unroll
+                    for (int i = 0; i < 16; i++)
+                        if (i < valid) {
+                            const int n = n_first + i;
+                            orow[(n % ep.perm_p) * ep.perm_c + n / ep.perm_p] = v[i];
+                        }
+                } else if (valid == 16 && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
 #pragma unroll
                     for (int i = 0; i < 4; i++)
                         reinterpret_cast<float4*>(crow)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -327,11 +402,30 @@ int tc_linear_fwd(const float* x, const float* w, const float* b, float* y, int 
     return dispatch<false, false, kEpiBiasAct>(x, m, k, w, n, k, ep, m, n, k, st);
 }
 
+bool tc_linear_softmax_supported(int m, int n, int k, int ld) { return m > 0 && n > 0 && n <= 16 && ld >= n && ld <= 16 && k > 0 && k % 4 == 0; }
+
+int tc_linear_softmax_xent(const float* x, const float* w, const float* b, const uint8_t* labels, float* probs, float* dz,
+                           float* metrics, int m, int n, int k, int ld, cudaStream_t st) {
+    if (!aligned16(x) || !aligned16(w)) return set_error(kInvalidValue, "tc_linear_softmax_xent: operands must be 16-byte aligned");
+    EpiArgs ep{};
+    ep.C = probs; ep.ldc = ld; ep.bias = b; ep.labels = labels; ep.dz = dz; ep.metrics = metrics;
+    CUtensorMap ta, tb;
+    if (int rc = make_operand_map(&ta, x, false, m, k, k, BLOCK_M)) return rc;
+    if (int rc = make_operand_map(&tb, w, false, n, k, k, 16)) return rc;
+    return launch_cfg<16, false, false, kEpiSoftmax>(ta, tb, ep, m, n, k, st);
+}
+
 int tc_linear_bwd_data(const float* dz, const float* w, const float* a_prev, int act_prev, float* dx, int m, int n, int k,
                        int lddz, cudaStream_t st) {
+    return tc_linear_bwd_data_permuted(dz, w, a_prev, act_prev, dx, m, n, k, lddz, 0, 0, st);
+}
+
+int tc_linear_bwd_data_permuted(const float* dz, const float* w, const float* a_prev, int act_prev, float* dx, int m, int n,
+                                int k, int lddz, int perm_p, int perm_c, cudaStream_t st) {
     if (!aligned16(dz) || !aligned16(w)) return set_error(kInvalidValue, "tc_linear_bwd_data: operands must be 16-byte aligned");
+    if (perm_p > 0 && perm_p * perm_c != k) return set_error(kInvalidValue, "tc_linear_bwd_data: permutation %dx%d does not cover %d columns", perm_p, perm_c, k);
     EpiArgs ep{};
-    ep.C = dx; ep.ldc = k; ep.aux = a_prev; ep.ld_aux = k; ep.act = act_prev;
+    ep.C = dx; ep.ldc = k; ep.aux = a_prev; ep.ld_aux = k; ep.act = act_prev; ep.perm_p = perm_p; ep.perm_c = perm_c;
     // D[m][k_in] = sum over n_out: A = dz [m][n_out] K-major; B(n = k_in, k = n_out) = w[n_out][k_in] N-major.
     return dispatch<false, true, kEpiActGrad>(dz, m, lddz, w, k, k, ep, m, k, n, st);
 }

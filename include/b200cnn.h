@@ -67,9 +67,15 @@ int b200cnn_conv2d_bwd_weight(const float* dz, const void* x, int x_is_u8, float
  * written per sample CHW-flattened with row stride ldy (what the next FC layer reads, cnn.c:116-121). */
 int b200cnn_conv3x3_fwd_nhwc(const float* x_nhwc, const float* w, const float* b, float* y, int ldy,
                              const b200cnn_conv_shape* s, int act, b200cnn_stream stream);
-/* 3x3 / stride 2 / pad 1, 32 -> 16 channels: dx = conv_transpose(dz, w) * act'(a_prev). */
-int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev,
+/* 3x3 / stride 2 / pad 1, 32 -> 16 channels: dx = conv_transpose(dz, w) * act'(a_prev).  dz is NHWC (TMA-fed)
+ * or, with dz_is_chw, the CHW gradient an FC layer produces for its flattened input (gathered in-kernel). */
+int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
                                     float* dx_nhwc, const b200cnn_conv_shape* s, b200cnn_stream stream);
+/* dw (OIHW) / db for NHWC activations: x NHWC (or a 1-channel image, uint8 allowed), dz NHWC or CHW.
+ * Register-tiled CUDA-core kernel + fixed-order reduction of per-block partial sums held in `scratch`. */
+size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s);
+int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const float* dz, int dz_is_chw, float* dw, float* db,
+                                   int accumulate, void* scratch, const b200cnn_conv_shape* s, b200cnn_stream stream);
 
 /* ---- fully connected (K4, K6) ------------------------------------------------------------- */
 /* y[m][n] = act(sum_k x[m][k] w[n][k] + b[n]); ldy = row stride of y in floats (>= n).
@@ -90,6 +96,12 @@ int b200cnn_linear_bwd_weight(const float* dz, const float* x, float* dw, float*
  * Replaces cnn.c:125-143 and :285-286. */
 int b200cnn_softmax_xent(const float* logits, const uint8_t* labels, float* probs, float* dz, float* metrics,
                          int m, int n, int ld, b200cnn_stream stream);
+
+/* Output layer fused with the loss (K5): probs[m][ld] = softmax(x W^T + b) over the first n columns,
+ * dz = probs - onehot(labels) (NULL labels: probabilities only), metrics as above.  On the tcgen05 path the
+ * softmax runs in the GEMM epilogue on the accumulator row (n <= 16); otherwise two CUDA-core kernels. */
+int b200cnn_linear_softmax_xent(const float* x, const float* w, const float* b, const uint8_t* labels, float* probs,
+                                float* dz, float* metrics, int m, int n, int k, int ld, b200cnn_stream stream);
 
 /* ---- max pooling (K7; not in the reference) ------------------------------------------------ */
 int b200cnn_maxpool_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride,

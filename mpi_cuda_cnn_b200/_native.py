@@ -124,11 +124,14 @@ def cuda():
     _sig(lib, "b200cnn_conv2d_bwd_weight_scratch_bytes", sz, cs)
     _sig(lib, "b200cnn_conv2d_bwd_weight", i, vp, vp, i, vp, vp, i, vp, cs, vp)
     _sig(lib, "b200cnn_conv3x3_fwd_nhwc", i, vp, vp, vp, vp, i, cs, i, vp)
-    _sig(lib, "b200cnn_conv3x3s2_bwd_data_nhwc", i, vp, vp, vp, i, vp, cs, vp)
+    _sig(lib, "b200cnn_conv3x3s2_bwd_data_nhwc", i, vp, i, vp, vp, i, vp, cs, vp)
+    _sig(lib, "b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes", sz, cs)
+    _sig(lib, "b200cnn_conv2d_bwd_weight_nhwc", i, vp, i, vp, i, vp, vp, i, vp, cs, vp)
     _sig(lib, "b200cnn_linear_fwd", i, vp, vp, vp, vp, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_linear_bwd_data", i, vp, vp, vp, i, vp, i, i, i, i, vp)
     _sig(lib, "b200cnn_linear_bwd_weight", i, vp, vp, vp, vp, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_softmax_xent", i, vp, vp, vp, vp, vp, i, i, i, vp)
+    _sig(lib, "b200cnn_linear_softmax_xent", i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, vp)
     _sig(lib, "b200cnn_maxpool_fwd", i, vp, vp, vp, i, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_maxpool_bwd", i, vp, vp, vp, i, vp, i, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_sgd_update", i, vp, vp, sz, f, i, vp)

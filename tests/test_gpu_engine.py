@@ -27,7 +27,11 @@ def test_forward_backward_step_vs_torch(pool, backend):
     from mpi_cuda_cnn_b200.ops import functional as F200
 
     F200.set_backend(backend)
+    # TF32 operands (10-bit mantissa, truncated by the tensor core) through five chained GEMM layers:
+    # activations agree to <0.6 %, the conv weight / bias gradients (sums with heavy cancellation) to <4 % of their largest entry
+    # (measured per tensor by tools/diag_engine.py: 0.3-2.2 %).
     tol = 2e-4 if backend == "simt" else 6e-3
+    gtol = 2e-4 if backend == "simt" else 4e-2
     B = 64
     eng = Engine(pool_layers() if pool else mnist_layers(), max_batch=B)
     cpu = eng.init_params(seed=0)
@@ -51,7 +55,7 @@ def test_forward_backward_step_vs_torch(pool, backend):
     o = 0
     for p in model.param_list():  # per-tensor, so a small tensor cannot hide behind a big one
         n = p.numel()
-        assert _rel(g[o:o + n], gr[o:o + n]) < tol, f"grad of tensor at offset {o}"
+        assert _rel(g[o:o + n], gr[o:o + n]) < gtol, f"grad of tensor at offset {o}"
         o += n
     before = eng.get_params()
     eng.sgd(0.1 / B)

@@ -31,7 +31,32 @@ for n in (2, 256, 7):
     dz_nhwc = dz.permute(0, 2, 3, 1).contiguous(); a1_nhwc = a1.permute(0, 2, 3, 1).contiguous()
     dx = torch.full((n, 14, 14, 16), 7.0, device="cuda")
     shp = N.ConvShape(n, 16, 14, 14, 32, 7, 7, 3, 1, 2)
-    rc = lib.b200cnn_conv3x3s2_bwd_data_nhwc(p(dz_nhwc), p(w), p(a1_nhwc), N.ACT_RELU, p(dx), C.byref(shp), st)
+    rc = lib.b200cnn_conv3x3s2_bwd_data_nhwc(p(dz_nhwc), 0, p(w), p(a1_nhwc), N.ACT_RELU, p(dx), C.byref(shp), st)
     torch.cuda.synchronize()
     want = F.conv_transpose2d(dz, w, None, 2, 1, output_padding=1) * (a1 > 0)
     stat(f"bwd_data n{n} rc={rc} {lib.b200cnn_last_error().decode()[:30]}", dx.permute(0, 3, 1, 2), want)
+    dx2 = torch.full((n, 14, 14, 16), 7.0, device="cuda")
+    rc = lib.b200cnn_conv3x3s2_bwd_data_nhwc(p(dz), 1, p(w), p(a1_nhwc), N.ACT_RELU, p(dx2), C.byref(shp), st)
+    stat(f"bwd_data(chw dz) n{n} rc={rc}", dx2.permute(0, 3, 1, 2), want)
+    # backward-weight, NHWC x + CHW / NHWC dz
+    nbytes = lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp))
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    dzm = dz * 1.0
+    wr = w.clone().requires_grad_(); a1r = a1.clone()
+    y = F.conv2d(a1r, wr, None, 2, 1); y.backward(dzm)
+    for chw, src in ((1, dz), (0, dz_nhwc)):
+        dw = torch.full_like(w, 7.0); db = torch.full((32,), 7.0, device="cuda")
+        rc = lib.b200cnn_conv2d_bwd_weight_nhwc(p(a1_nhwc), 0, p(src), chw, p(dw), p(db), 0, p(scratch), C.byref(shp), st)
+        stat(f"bwd_weight nhwc dz_chw={chw} n{n} rc={rc}", dw, wr.grad)
+        stat(f"bwd_bias   nhwc dz_chw={chw} n{n}", db, dz.sum((0, 2, 3)))
+    # first conv: 1 input channel (uint8 image), dz NHWC [n][14][14][16]
+    x8 = torch.randint(0, 256, (n, 1, 28, 28), device="cuda", dtype=torch.uint8)
+    dz1 = torch.randn(n, 16, 14, 14, device="cuda"); dz1_nhwc = dz1.permute(0, 2, 3, 1).contiguous()
+    shp1 = N.ConvShape(n, 1, 28, 28, 16, 14, 14, 3, 1, 2)
+    w1 = torch.zeros(16, 1, 3, 3, device="cuda", requires_grad=True)
+    F.conv2d(x8.float() / 255.0, w1, None, 2, 1).backward(dz1)
+    scratch = torch.empty(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp1)), dtype=torch.uint8, device="cuda")
+    dw1 = torch.full((16, 1, 3, 3), 7.0, device="cuda"); db1 = torch.full((16,), 7.0, device="cuda")
+    rc = lib.b200cnn_conv2d_bwd_weight_nhwc(p(x8), 1, p(dz1_nhwc), 0, p(dw1), p(db1), 0, p(scratch), C.byref(shp1), st)
+    stat(f"bwd_weight c1 u8 n{n} rc={rc}", dw1, w1.grad)
+    stat(f"bwd_bias   c1 u8 n{n}", db1, dz1.sum((0, 2, 3)))
