@@ -211,6 +211,8 @@ def run_b200(args):
             "config": {"model": MODEL, "global_batch": BATCH * world, "seq_len": None, "parallelism": f"dp{world}",
                        "per_gpu_batch": BATCH, "update": ("fused p2p allreduce+sgd (%s)" % args.algo) if mode == "fused" else "nccl allreduce + scale/sgd kernel",
                        "cuda_graph": use_graph, "backend": args.backend,
+                       "region": (trainer.comm.region.kind if trainer is not None and trainer.comm is not None else None),
+                       "nvls_multicast": (trainer.comm.has_multicast if trainer is not None and trainer.comm is not None else None),
                        "l2_policy": f"inputs larger than L2: each step gathers a random batch from a {n_data * 784 / 2**20:.0f} MiB device-resident set",
                        "final_mse_metric": m_dev["mse_sum"] / max(m_dev["count"], 1), "final_accuracy": m_dev["correct"] / max(m_dev["count"], 1)},
             "clocks": {"sm_mhz": ck["sm_mhz"], "sm_max_mhz": ck["sm_max_mhz"], "reasons": ck["reasons"], "samples": ck["samples"]},

@@ -30,6 +30,33 @@ inline cudaStream_t as_stream(b200cnn_stream s) { return static_cast<cudaStream_
 
 constexpr int kInvalidValue = 1;  // cudaErrorInvalidValue
 
+// ---- programmatic dependent launch (PDL) -----------------------------------------------------------
+// Every kernel of the training step is launched with programmatic stream serialization: the next
+// kernel in the stream may be scheduled while this one still runs, so its prologue (barrier init, TMEM
+// allocation, tensor-map prefetch, launch latency itself) overlaps our body.  Contract: a kernel calls
+// pdl_wait() before its first global-memory access (blocks until the previous kernel has completed and
+// its writes are visible) and pdl_launch_dependents() right after, which lets the NEXT kernel start its
+// own prologue.  At most two kernels of a stream are ever in flight.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // B200CNN_PDL=0 in the environment turns the launch attribute off
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 // Derivative of an activation expressed through its OUTPUT value, like the reference's

@@ -37,6 +37,8 @@ conv2d_fwd_kernel(const TIn* __restrict__ x, const float* __restrict__ w, const 
     extern __shared__ __align__(16) float ws[];
     const int ckk = s.c * s.k * s.k;
     const int oc0 = blockIdx.y * kOcTile;
+    pdl_wait();
+    pdl_launch_dependents();
     for (int i = threadIdx.x; i < ckk * kOcTile; i += blockDim.x) {
         const int j = i / kOcTile, o = i % kOcTile;
         ws[i] = (oc0 + o < s.oc) ? __ldg(w + size_t(oc0 + o) * ckk + j) : 0.0f;
@@ -221,6 +223,8 @@ conv2d_bwd_weight_reduce_kernel(const float* __restrict__ partials, float* __res
     const int j = blockIdx.x * 32 + lane;
     const int nout = nw + nb;
     float a = 0.0f;
+    pdl_wait();
+    pdl_launch_dependents();
     if (j < nout) {
         int c = slice;
         for (; c + 3 * kRedSlices < nchunks; c += 4 * kRedSlices) {
@@ -268,7 +272,8 @@ using namespace b200cnn;
 namespace b200cnn {
 int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks, int nw, int nb, int accumulate,
                          cudaStream_t st) {
-    conv2d_bwd_weight_reduce_kernel<<<ceil_div(nw + nb, 32), 32 * kRedSlices, 0, st>>>(partials, dw, db, chunks, nw, nb, accumulate);
+    B200CNN_CUDA(launch_kernel(conv2d_bwd_weight_reduce_kernel, dim3(ceil_div(nw + nb, 32)), dim3(32 * kRedSlices), 0, st, partials, dw, db,
+                               chunks, nw, nb, accumulate));
     B200CNN_CHECK_LAUNCH("conv2d_bwd_weight(reduce)");
     return 0;
 }
@@ -288,11 +293,11 @@ int b200cnn::simt_conv2d_fwd(const void* x, int x_is_u8, const float* w, const f
     if (smem > 48 * 1024) return set_error(kInvalidValue, "conv2d_fwd: c*k*k = %d too large for the direct kernel", s->c * s->k * s->k);
     const dim3 grid(ceil_div(s->n * s->oh * s->ow, kConvThreads), ceil_div(s->oc, kOcTile));
     if (x_is_u8)
-        conv2d_fwd_kernel<uint8_t><<<grid, kConvThreads, smem, stream>>>(static_cast<const uint8_t*>(x), w, b, y, *s, act,
-                                                                         1.0f / 255.0f, nhwc_out);
+        B200CNN_CUDA(launch_kernel(conv2d_fwd_kernel<uint8_t>, grid, dim3(kConvThreads), smem, stream, static_cast<const uint8_t*>(x),
+                                   w, b, y, *s, act, 1.0f / 255.0f, nhwc_out));
     else
-        conv2d_fwd_kernel<float><<<grid, kConvThreads, smem, stream>>>(static_cast<const float*>(x), w, b, y, *s, act, 1.0f,
-                                                                       nhwc_out);
+        B200CNN_CUDA(launch_kernel(conv2d_fwd_kernel<float>, grid, dim3(kConvThreads), smem, stream, static_cast<const float*>(x), w,
+                                   b, y, *s, act, 1.0f, nhwc_out));
     B200CNN_CHECK_LAUNCH("conv2d_fwd");
     return 0;
 }

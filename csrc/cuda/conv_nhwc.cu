@@ -43,6 +43,8 @@ conv_bwd_weight_nhwc_kernel(const float* __restrict__ x, const float* __restrict
     const bool bias_thread = worker && tap == 0 && c4 == 0;
 
     const int n0 = blockIdx.x * spb, ns = min(spb, s.n - n0);
+    pdl_wait();
+    pdl_launch_dependents();
     float* xs = sm;                       // [ns][h][w][C]
     float* gs = sm + size_t(spb) * in_sz; // [ns][pix][OC]
     {
@@ -126,6 +128,8 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
     float* xs = sm;                         // [ns][in_pad]
     float* gs = sm + size_t(spb) * in_pad;  // [ns][pix][OC]
     float* red = gs + size_t(spb) * out_sz; // [kC1Slices][nout]
+    pdl_wait();
+    pdl_launch_dependents();
     for (int i = t; i < ns * in_sz; i += blockDim.x)
         xs[(i / in_sz) * in_pad + i % in_sz] = cvt_in<TIn>(__ldg(x + size_t(n0) * in_sz + i), in_scale);
     {
@@ -200,10 +204,10 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         if (threads > 1024 || smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: layer too large for the single-channel kernel");
         if (x_is_u8) {
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-            conv_bwd_weight_c1_nhwc_kernel<uint8_t><<<chunks, threads, smem, st>>>(static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f);
+            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, dim3(chunks), dim3(threads), smem, st, static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f));
         } else {
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-            conv_bwd_weight_c1_nhwc_kernel<float><<<chunks, threads, smem, st>>>(static_cast<const float*>(x), dz, partials, *s, spb, 1.0f);
+            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f));
         }
     } else {
         const int work = (s->oc / 4) * (s->c / 4) * kk;
@@ -211,7 +215,7 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         const size_t smem = size_t(spb) * (size_t(s->h) * s->w * s->c + size_t(s->oh) * s->ow * s->oc) * sizeof(float);
         if (smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: samples do not fit shared memory");
         if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_nhwc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-        conv_bwd_weight_nhwc_kernel<<<chunks, threads, smem, st>>>(static_cast<const float*>(x), dz, partials, *s, spb, dz_chw);
+        B200CNN_CUDA(launch_kernel(conv_bwd_weight_nhwc_kernel, dim3(chunks), dim3(threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, dz_chw));
     }
     B200CNN_CHECK_LAUNCH("nhwc_conv_bwd_weight");
     return reduce_conv_partials(partials, dw, db, chunks, nw, s->oc, accumulate, st);

@@ -233,6 +233,8 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
 
 __global__ void sgd_dev_lr_kernel(float* __restrict__ w, const float* __restrict__ g, size_t n4,
                                   const float* __restrict__ lr_dev) {
+    pdl_wait();
+    pdl_launch_dependents();
     const float lr = *lr_dev;
     float4* w4 = reinterpret_cast<float4*>(w);
     const float4* g4 = reinterpret_cast<const float4*>(g);
@@ -251,8 +253,8 @@ int enqueue_update(b200cnn_engine* e, cudaStream_t st, int* launches) {
     if (e->comm) return comm_join(e->comm, st);  // per-layer fused updates already enqueued
     const size_t n4 = e->flat_floats / 4;
     const int blocks = int(std::min<size_t>((n4 + 255) / 256, 148 * 4));
-    sgd_dev_lr_kernel<<<blocks, 256, 0, st>>>(e->params, cur_grads(e), n4, e->lr_dev);
-    B200CNN_CHECK_LAUNCH("engine sgd");
+    B200CNN_CUDA(launch_kernel(sgd_dev_lr_kernel, dim3(blocks), dim3(256), 0, st, e->params, static_cast<const float*>(cur_grads(e)), n4,
+                               static_cast<const float*>(e->lr_dev)));
     if (launches) (*launches)++;
     return 0;
 }

@@ -1,6 +1,7 @@
 // Error reporting and build facts of the GPU library.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -14,6 +15,14 @@ int set_error(int code, const char* fmt, ...) {
     vsnprintf(g_error, sizeof(g_error), fmt, ap);
     va_end(ap);
     return code ? code : kInvalidValue;
+}
+
+bool pdl_enabled() {
+    static const bool on = [] {
+        const char* v = getenv("B200CNN_PDL");
+        return !(v && v[0] == '0');
+    }();
+    return on;
 }
 
 }  // namespace b200cnn

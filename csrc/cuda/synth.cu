@@ -42,6 +42,8 @@ __global__ void gather_batch_kernel(const uint8_t* __restrict__ images, const ui
                                     int batch, uint64_t seed, uint64_t step, uint32_t shard_begin, uint32_t shard_len) {
     const int b = blockIdx.x;
     if (b >= batch) return;
+    pdl_wait();
+    pdl_launch_dependents();
     const uint32_t idx = shard_begin + uint32_t(mix64(mix64(seed ^ (step * 0x9e3779b97f4a7c15ull)) + b) % shard_len);
     if (threadIdx.x == 0) out_labels[b] = labels[idx];
     const uint8_t* src = images + size_t(idx) * item_bytes;
@@ -65,9 +67,8 @@ extern "C" int b200cnn_gather_batch(const uint8_t* images, const uint8_t* labels
                                     uint32_t shard_begin, uint32_t shard_len, b200cnn_stream stream) {
     if (batch <= 0 || item_bytes <= 0 || shard_len == 0 || shard_begin + shard_len > n_items)
         return set_error(kInvalidValue, "gather_batch: bad shard [%u, %u) of %u", shard_begin, shard_begin + shard_len, n_items);
-    gather_batch_kernel<<<batch, 64, 0, as_stream(stream)>>>(images, labels, item_bytes, out_images, out_labels, batch,
-                                                             seed, step, shard_begin, shard_len);
-    B200CNN_CHECK_LAUNCH("gather_batch");
+    B200CNN_CUDA(launch_kernel(gather_batch_kernel, dim3(batch), dim3(64), 0, as_stream(stream), images, labels, item_bytes,
+                               out_images, out_labels, batch, seed, step, shard_begin, shard_len));
     return 0;
 }
 

@@ -71,6 +71,8 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a)
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -83,10 +85,19 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a)
     } else if (warp >= 2) {
         // Weights: OIHW -> per-tap K-major [oc][c] tiles in the 64-byte-swizzle layout
         // (16-byte chunk index ^= (row >> 1) & 3, cute Swizzle<2,4,3>).
-        for (int i = threadIdx.x - 64; i < OC * kCin * kTaps; i += kConvThreads - 64) {
-            const int t = i % kTaps, c = (i / kTaps) % kCin, oc = i / (kTaps * kCin);  // i walks OIHW linearly
-            const int chunk = (c >> 2) ^ ((oc >> 1) & 3);
-            *reinterpret_cast<float*>(b_tiles + t * kBTile + oc * 64 + chunk * 16 + (c & 3) * 4) = __ldg(a.w + i);
+        constexpr int kW = OC * kCin * kTaps, kStride = kConvThreads - 64;
+        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += 4 * kStride) {  // i walks OIHW linearly; 4 loads in flight
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i = i0 + u * kStride;
+                if (i >= kW) break;
+                const int t = i % kTaps, c = (i / kTaps) % kCin, oc = i / (kTaps * kCin);
+                const int chunk = (c >> 2) ^ ((oc >> 1) & 3);
+                *reinterpret_cast<float*>(b_tiles + t * kBTile + oc * 64 + chunk * 16 + (c & 3) * 4) = v[u];
+            }
         }
         fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor-core (async) proxy
     }
@@ -179,23 +190,38 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
 
     if (a.dz_chw) {
         // dz arrives CHW (the FC layer's gradient w.r.t. its flattened input): transpose it on the fly into
         // the four shifted K-major tiles, 128-byte rows, 128B swizzle.  Reads are coalesced along the pixel
         // index; each thread writes one 16-byte chunk (4 channels of one pixel), conflict-free thanks to
         // the swizzle.
-        for (int i = threadIdx.x; i < 4 * (OC / 4) * kTileRows; i += kConvThreads) {
-            const int r = i % kTileRows, oc4 = (i / kTileRows) % (OC / 4), sft = i / (kTileRows * (OC / 4));
-            if (r >= rows) continue;
-            const int g = r / pix, p = r % pix;
-            const int jj = p / a.ow + (sft >> 1), ix = p % a.ow + (sft & 1);
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (jj < a.oh && ix < a.ow) {
-                const float* src = a.dz_chw + (size_t(n0 + g) * OC + oc4 * 4) * pix + jj * a.ow + ix;
-                v = make_float4(__ldg(src), __ldg(src + pix), __ldg(src + 2 * pix), __ldg(src + 3 * pix));
+        constexpr int kItems = 4 * (OC / 4) * kTileRows;
+        for (int i0 = threadIdx.x; i0 < kItems; i0 += 4 * kConvThreads) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {  // issue every load of the batch before the first store
+                const int i = i0 + u * kConvThreads;
+                const int r = i % kTileRows, oc4 = (i / kTileRows) % (OC / 4), sft = i / (kTileRows * (OC / 4));
+                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (i < kItems && r < rows) {
+                    const int g = r / pix, p = r % pix;
+                    const int jj = p / a.ow + (sft >> 1), ix = p % a.ow + (sft & 1);
+                    if (jj < a.oh && ix < a.ow) {
+                        const float* src = a.dz_chw + (size_t(n0 + g) * OC + oc4 * 4) * pix + jj * a.ow + ix;
+                        v[u] = make_float4(__ldg(src), __ldg(src + pix), __ldg(src + 2 * pix), __ldg(src + 3 * pix));
+                    }
+                }
             }
-            *reinterpret_cast<float4*>(a_tiles + sft * kATile + r * 128 + ((oc4 ^ (r & 7)) << 4)) = v;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i = i0 + u * kConvThreads;
+                const int r = i % kTileRows, oc4 = (i / kTileRows) % (OC / 4), sft = i / (kTileRows * (OC / 4));
+                if (i < kItems && r < rows)
+                    *reinterpret_cast<float4*>(a_tiles + sft * kATile + r * 128 + ((oc4 ^ (r & 7)) << 4)) = v[u];
+            }
         }
     } else if (warp == 0) {
         if (lane == 0) {
@@ -208,10 +234,19 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
     if (warp >= 2) {
         // Weights per tap as the B operand [n = c][k = oc], K-major 128-byte rows, 128B swizzle
         // (16-byte chunk ^= row & 7).
-        for (int i = threadIdx.x - 64; i < OC * C * kTaps; i += kConvThreads - 64) {
-            const int t = i % kTaps, c = (i / kTaps) % C, oc = i / (kTaps * C);
-            const int chunk = (oc >> 2) ^ (c & 7);
-            *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = __ldg(a.w + i);
+        constexpr int kW = OC * C * kTaps, kStride = kConvThreads - 64;
+        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += 4 * kStride) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i = i0 + u * kStride;
+                if (i >= kW) break;
+                const int t = i % kTaps, c = (i / kTaps) % C, oc = i / (kTaps * C);
+                const int chunk = (oc >> 2) ^ (c & 7);
+                *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = v[u];
+            }
         }
     }
     fence_proxy_async_smem();
@@ -322,7 +357,7 @@ int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y
             B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));      \
             configured = true;                                                                                    \
         }                                                                                                         \
-        kern<<<grid, kConvThreads, smem, st>>>(tm, a);                                                            \
+        B200CNN_CUDA(launch_kernel(kern, dim3(grid), dim3(kConvThreads), smem, st, tm, a));                          \
     } while (0)
     if (s->oc == 16) B200CNN_LAUNCH_FWD(16);
     else if (s->oc == 32) B200CNN_LAUNCH_FWD(32);
@@ -357,7 +392,7 @@ int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const 
         B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         configured = true;
     }
-    kern<<<ceil_div(s->n, group), kConvThreads, smem, st>>>(tm, a);
+    B200CNN_CUDA(launch_kernel(kern, dim3(ceil_div(s->n, group)), dim3(kConvThreads), smem, st, tm, a));
     B200CNN_CHECK_LAUNCH("tc_conv3x3s2_bwd_data");
     return 0;
 }

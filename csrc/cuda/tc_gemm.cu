@@ -131,6 +131,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();               // everything above overlapped the previous kernel's tail
+    pdl_launch_dependents();  // let the next kernel begin its own prologue
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -353,18 +355,17 @@ int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const EpiArgs& ep, 
         configured = true;
     }
     const dim3 grid(ceil_div(N, BLOCK_N), ceil_div(M, BLOCK_M));
-    kern<<<grid, kThreads, smem, st>>>(ta, tb, ep, M, N, K);
-    B200CNN_CHECK_LAUNCH("tc_gemm");
+    B200CNN_CUDA(launch_kernel(kern, grid, dim3(kThreads), smem, st, ta, tb, ep, M, N, K));
     return 0;
 }
 
-// Tile width: the widest N tile that still yields >= 48 CTAs, because at these sizes a CTA's time is
+// Tile width: the widest N tile that still yields >= 96 CTAs, because at these sizes a CTA's time is
 // its own operand stream and more, narrower CTAs finish sooner.
 int pick_block_n(int M, int N, int min_bn) {
     const int mt = ceil_div(M, BLOCK_M);
     for (int bn : {128, 64, 32, 16}) {
         if (bn < min_bn) break;
-        if (mt * ceil_div(N, bn) >= 48) return bn;
+        if (mt * ceil_div(N, bn) >= 96) return bn;
     }
     return min_bn;
 }
