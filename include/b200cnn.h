@@ -62,6 +62,19 @@ size_t b200cnn_conv2d_bwd_weight_scratch_bytes(const b200cnn_conv_shape* s);
 int b200cnn_conv2d_bwd_weight(const float* dz, const void* x, int x_is_u8, float* dw, float* db, int accumulate,
                               void* scratch, const b200cnn_conv_shape* s, b200cnn_stream stream);
 
+/* Same result as b200cnn_conv2d_bwd_weight for callers that may not allocate device memory (a plug-in
+ * inside a host application that owns all of the GPU's memory, a latency-bound loop that cannot afford
+ * cudaMalloc's device synchronisation, a process with a fixed memory map).  It has no counterpart in the
+ * reference.  The partial sums live in an 8 MiB array built into the library (present on every GPU that
+ * loads it, until exit); the function allocates and frees nothing.  Shapes that need more scratch than
+ * B200CNN_NOALLOC_SCRATCH_BYTES are refused with an error.  The first call on each device resolves the
+ * array's address (do it before any stream capture); all calls on a device share the array, so calls
+ * that may overlap on the GPU must be ordered by the caller. */
+#define B200CNN_NOALLOC_SCRATCH_BYTES (8u << 20)
+size_t b200cnn_conv2d_bwd_weight_noalloc_capacity(void);
+int b200cnn_conv2d_bwd_weight_noalloc(const float* dz, const void* x, int x_is_u8, float* dw, float* db, int accumulate,
+                                      const b200cnn_conv_shape* s, b200cnn_stream stream);
+
 /* Tensor-core (tcgen05) implicit-GEMM convolutions on NHWC activations: the engine's fast path for
  * 3x3 convolutions whose input has 16 channels.  x / dz / dx / a_prev are NHWC; the forward output is
  * written per sample CHW-flattened with row stride ldy (what the next FC layer reads, cnn.c:116-121). */

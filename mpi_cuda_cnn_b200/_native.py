@@ -123,6 +123,8 @@ def cuda():
     _sig(lib, "b200cnn_conv2d_bwd_data", i, vp, vp, vp, i, vp, cs, vp)
     _sig(lib, "b200cnn_conv2d_bwd_weight_scratch_bytes", sz, cs)
     _sig(lib, "b200cnn_conv2d_bwd_weight", i, vp, vp, i, vp, vp, i, vp, cs, vp)
+    _sig(lib, "b200cnn_conv2d_bwd_weight_noalloc_capacity", sz)
+    _sig(lib, "b200cnn_conv2d_bwd_weight_noalloc", i, vp, vp, i, vp, vp, i, cs, vp)
     _sig(lib, "b200cnn_conv3x3_fwd_nhwc", i, vp, vp, vp, vp, i, cs, i, vp)
     _sig(lib, "b200cnn_conv3x3s2_bwd_data_nhwc", i, vp, i, vp, vp, i, vp, cs, vp)
     _sig(lib, "b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes", sz, cs)
