@@ -66,16 +66,16 @@ $(LIBDIR)/libb200cnn_cuda.so: $(CUDA_OBJS)
 	@mkdir -p $(LIBDIR)
 	$(NVCC) $(SM_ARCH) -shared -o $@ $^ -lcudart
 
-$(BINDIR)/cudacnn: csrc/apps/cudacnn_main.cpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o
+$(BINDIR)/cudacnn: csrc/apps/cudacnn_main.cpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o
 	@mkdir -p $(BINDIR)
-	$(CXX) $(CXXFLAGS) -Iinclude -I/usr/local/cuda/include -o $@ csrc/apps/cudacnn_main.cpp $(OBJDIR)/cpu/idx.o \
+	$(CXX) $(CXXFLAGS) -Iinclude -I/usr/local/cuda/include -o $@ csrc/apps/cudacnn_main.cpp $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o \
 	    -L$(LIBDIR) -lb200cnn_cuda -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$$ORIGIN/../$(LIBDIR)'
 
 sass: $(LIBDIR)/libb200cnn_cuda.so
-	@mkdir -p profiles/sass
-	cuobjdump -sass $< > profiles/sass/libb200cnn_cuda.sass
-	cuobjdump -res-usage $< > profiles/sass/libb200cnn_cuda.resources.txt 2>&1 || true
-	python tools/sass_summary.py profiles/sass/libb200cnn_cuda.sass > profiles/sass/SUMMARY.md
+	@mkdir -p profiles/sass $(OBJDIR)
+	cuobjdump -sass $< > $(OBJDIR)/libb200cnn_cuda.sass
+	cuobjdump -res-usage $< > profiles/sass/resources.txt 2>&1 || true
+	python tools/sass_summary.py $(OBJDIR)/libb200cnn_cuda.sass profiles/sass > profiles/sass/SUMMARY.md
 
 DATADIR ?= build/data
 get_mnist: $(BINDIR)/mkidx
