@@ -65,6 +65,9 @@ struct b200cnn_engine {
     int launches_per_step = 0;
     cudaStream_t side = nullptr;          // weight-gradient kernels run here, next to the data-gradient chain
     cudaEvent_t ev_dz = nullptr, ev_data = nullptr, ev_side = nullptr;
+    // Data-parallel update buckets: consecutive layers' slices are merged until a bucket holds kBucketFloats,
+    // so the number of cross-GPU flag exchanges per step is 2 instead of one per layer.
+    long bucket_lo = -1, bucket_hi = -1;
     bool last_fast = false;   // layout of layer 1's activations in the last forward (NHWC when true)
     bool fast_chain = false;  // conv(C_in=1) -> tc conv3x3 -> FC pattern: NHWC activations + tcgen05 convolutions
     int g_backend = -1;
@@ -143,13 +146,26 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
     return 0;
 }
 
-// Per-layer hook after that layer's gradients are complete: the data-parallel path launches the fused
-// all-reduce + SGD for the layer's slice right here so it overlaps the rest of backward.
-int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, cudaStream_t st, int* launches) {
+// Hook after a layer's gradients are complete (and its data-gradient kernel has been issued): the
+// data-parallel path adds the layer's slice to the current bucket and launches the fused all-reduce + SGD
+// for the bucket once it is big enough (or at the last layer), so it overlaps the rest of backward.  Layers
+// are visited last-to-first and their slices are adjacent in the flat buffer, so a bucket is one range.
+constexpr long kBucketFloats = 128 * 1024;  // 512 KiB
+
+int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, bool last, cudaStream_t st, int* launches) {
     if (!e->comm) return 0;
     const long begin = l.w_off;
     const long end = l.b_off + long(round_up(size_t(l.nb), kAlignFloats));
-    const int rc = comm_allreduce_sgd_slice(e->comm, size_t(begin), size_t(end - begin), e->lr_dev, st);
+    if (e->bucket_lo < 0) {
+        e->bucket_lo = begin;
+        e->bucket_hi = end;
+    } else {
+        e->bucket_lo = std::min(e->bucket_lo, begin);
+        e->bucket_hi = std::max(e->bucket_hi, end);
+    }
+    if (!last && e->bucket_hi - e->bucket_lo < kBucketFloats) return 0;
+    const int rc = comm_allreduce_sgd_slice(e->comm, size_t(e->bucket_lo), size_t(e->bucket_hi - e->bucket_lo), e->lr_dev, st);
+    e->bucket_lo = e->bucket_hi = -1;
     if (rc) return rc;
     if (launches) (*launches)++;
     return 0;
@@ -167,6 +183,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
     float* grads = cur_grads(e);
     const bool fast = use_fast_chain(e);
     cudaStream_t side = e->side;
+    e->bucket_lo = e->bucket_hi = -1;
     for (size_t li = L.size() - 1; li >= 1; li--) {
         EngineLayer& l = L[li];
         EngineLayer& p = L[li - 1];
@@ -222,7 +239,9 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
                 B200CNN_CUDA(cudaEventRecord(e->ev_data, st));
                 B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_data, 0));
             }
-            if ((rc = layer_grads_ready(e, l, side, launches))) return rc;
+            bool last = true;  // no parameterised layer below this one?
+            for (size_t lj = 1; lj < li; lj++) last = last && L[lj].nw == 0;
+            if ((rc = layer_grads_ready(e, l, last, side, launches))) return rc;
         }
     }
     // Join: everything on the side stream is ordered before whatever follows on `st`.
