@@ -118,7 +118,8 @@ constexpr int kC1Slices = 4;
 template <typename TIn>
 __global__ void __launch_bounds__(1024)
 conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restrict__ dz, float* __restrict__ partials,
-                               b200cnn_conv_shape s, int spb, float in_scale) {
+                               b200cnn_conv_shape s, int spb, float in_scale, float* __restrict__ dw, float* __restrict__ db,
+                               int accumulate, unsigned* __restrict__ counter) {
     extern __shared__ __align__(16) float sm[];
     const int OC = s.oc, kk = s.k * s.k, pix = s.oh * s.ow;
     const int in_sz = s.h * s.w, in_pad = (in_sz + 3) & ~3, out_sz = pix * OC;
@@ -168,6 +169,32 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
         const int oc = t % OC, tap = t / OC;
         partials[size_t(blockIdx.x) * nout + (t < nw ? oc * kk + tap : t)] = a;
     }
+    // The block that finishes last sums all partials in block order (fixed order => reproducible) and
+    // writes the gradient: no second kernel on the tail of the backward pass.
+    __shared__ unsigned is_last;
+    __threadfence();
+    __syncthreads();
+    if (t == 0) {
+        const unsigned done = atomicInc(counter, gridDim.x - 1);  // wraps back to 0 for the next call
+        is_last = (done == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    const int j = t % nout, part = t / nout;  // kC1Slices threads per output again
+    if (part < kC1Slices) {
+        float a = 0.f;
+        for (int c = part; c < int(gridDim.x); c += kC1Slices) a += __ldcg(partials + size_t(c) * nout + j);
+        red[part * nout + j] = a;
+    }
+    __syncthreads();
+    if (t < nout) {
+        float a = red[t];
+#pragma unroll
+        for (int sl = 1; sl < kC1Slices; sl++) a += red[sl * nout + t];
+        float* dst = t < nw ? (dw ? dw + t : nullptr) : (db ? db + (t - nw) : nullptr);
+        if (dst) *dst = accumulate ? *dst + a : a;
+    }
 }
 
 }  // namespace
@@ -190,8 +217,10 @@ int nhwc_bwd_weight_chunks(int n, int* spb_out) {
 
 // x: NHWC float (or [n][h][w] uint8/float when c == 1); dz: NHWC, or CHW when dz_chw (c > 1 only).
 // dw OIHW, db [oc].  partials: chunks*(nw+oc) floats.
+// counter: one zero-initialised word used by the single-channel kernel's "last block reduces" step (it resets
+// itself); NULL = the word right after this layer's partials.
 int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
-                         float* partials, const b200cnn_conv_shape* s, cudaStream_t st) {
+                         float* partials, unsigned* counter_in, const b200cnn_conv_shape* s, cudaStream_t st) {
     if (!nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: unsupported shape");
     int spb = 1;
     const int chunks = nhwc_bwd_weight_chunks(s->n, &spb);
@@ -200,14 +229,16 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         if (dz_chw) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: CHW gradients are only read by the multi-channel kernel");
         const int nout = nw + s->oc;
         const int threads = ((nout * kC1Slices + 31) / 32) * 32;
+        // completion counter: the last 128 bytes of the partials area (zero at allocation, self-resetting)
+        unsigned* counter = counter_in ? counter_in : reinterpret_cast<unsigned*>(partials + size_t(chunks) * nout);
         const size_t smem = (size_t(spb) * (((s->h * s->w + 3) & ~3) + size_t(s->oh) * s->ow * s->oc) + size_t(kC1Slices) * nout) * sizeof(float);
         if (threads > 1024 || smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: layer too large for the single-channel kernel");
         if (x_is_u8) {
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, dim3(chunks), dim3(threads), smem, st, static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f));
+            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, dim3(chunks), dim3(threads), smem, st, static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f, dw, db, accumulate, counter));
         } else {
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f));
+            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f, dw, db, accumulate, counter));
         }
     } else {
         const int work = (s->oc / 4) * (s->c / 4) * kk;
@@ -218,6 +249,7 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         B200CNN_CUDA(launch_kernel(conv_bwd_weight_nhwc_kernel, dim3(chunks), dim3(threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, dz_chw));
     }
     B200CNN_CHECK_LAUNCH("nhwc_conv_bwd_weight");
+    if (s->c == 1) return 0;  // reduced by its last block
     return reduce_conv_partials(partials, dw, db, chunks, nw, s->oc, accumulate, st);
 }
 

@@ -213,7 +213,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             const b200cnn_conv_shape s = conv_shape(p, l, batch);
             if (fast && li <= 2)
                 rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/li == 2, grads + l.w_off, grads + l.b_off, 0, e->scratch,
-                                          &s, side);
+                                          reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, side);
             else
                 rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0, e->scratch, &s, side);
             if (launches) (*launches) += 2;
@@ -344,12 +344,12 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
                         tc_linear_bwd_data_supported(max_batch, e->layers[3].nnodes, e->layers[2].nnodes, e->layers[3].ld);
         if (e->fast_chain) {
             const size_t chunks = size_t(nhwc_bwd_weight_chunks(max_batch, nullptr));
-            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[2].nw + e->layers[2].nb) * sizeof(float));
-            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float));
+            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[2].nw + e->layers[2].nb) * sizeof(float) + 128);
+            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float) + 128);
         }
     }
     e->scratch_bytes = round_up(scratch_bytes, 512);
-    const size_t arena_bytes = arena_floats * sizeof(float) + e->scratch_bytes + 1024;
+    const size_t arena_bytes = arena_floats * sizeof(float) + e->scratch_bytes + 1024;  // tail: metrics, lr, counters
     if (cudaMalloc(&e->arena, arena_bytes) != cudaSuccess || cudaMemset(e->arena, 0, arena_bytes) != cudaSuccess) {
         set_error(int(cudaGetLastError()), "engine_create: cannot allocate %zu bytes of activations", arena_bytes);
         delete e;

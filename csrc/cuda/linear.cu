@@ -70,8 +70,9 @@ extern "C" int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const 
                                               int accumulate, void* scratch, const b200cnn_conv_shape* s,
                                               b200cnn_stream stream) {
     if (!s || !scratch || !nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "conv2d_bwd_weight_nhwc: unsupported shape or missing scratch");
-    return nhwc_conv_bwd_weight(x, x_is_u8, dz, dz_is_chw, dw, db, accumulate, static_cast<float*>(scratch), s, as_stream(stream));
+    return nhwc_conv_bwd_weight(x, x_is_u8, dz, dz_is_chw, dw, db, accumulate, static_cast<float*>(scratch), nullptr, s, as_stream(stream));
 }
 extern "C" size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s) {
-    return size_t(nhwc_bwd_weight_chunks(s->n, nullptr)) * (size_t(s->oc) * s->c * s->k * s->k + s->oc) * sizeof(float);
+    // + 128 bytes: completion counter of the single-channel kernel (must be zero before the first use)
+    return size_t(nhwc_bwd_weight_chunks(s->n, nullptr)) * (size_t(s->oc) * s->c * s->k * s->k + s->oc) * sizeof(float) + 128;
 }

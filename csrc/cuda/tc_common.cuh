@@ -110,6 +110,21 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, float (&v)[16
     for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
 
+// ---- thread-block clusters / distributed shared memory -----------------------------------------------
+__device__ __forceinline__ void cluster_sync_all() {  // every thread of every CTA in the cluster
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// Address of `local` (a shared-memory address of THIS CTA's window) in CTA `rank` of the cluster.
+__device__ __forceinline__ uint32_t map_to_cluster_rank(uint32_t local, uint32_t rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(rank));
+    return remote;
+}
+__device__ __forceinline__ void st_cluster_f32x4(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared::cluster.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 // ---- descriptors -----------------------------------------------------------------------------------
 enum Swizzle : int { kSwNone = 0, kSw128Base32 = 1, kSw128 = 2, kSw64 = 4, kSw32 = 6 };  // UMMA::LayoutType encodings
 constexpr int kTmaSw128Atom32 = 12832;  // encode_tmap_f32 swizzle code for CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B

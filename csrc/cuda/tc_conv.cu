@@ -170,7 +170,8 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* a_tiles = smem;                  // 4 shifted views of dz
     uint8_t* b_tiles = smem + 4 * kATile;     // 9 taps
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + kTaps * kBTile);
+    float* stage = reinterpret_cast<float*>(b_tiles + kTaps * kBTile);  // [rows][OC] staging of CHW gradients
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stage) + kTileRows * OC * 4);
     uint64_t* tmem_full_bar = full_bar + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
@@ -198,30 +199,28 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
         // the four shifted K-major tiles, 128-byte rows, 128B swizzle.  Reads are coalesced along the pixel
         // index; each thread writes one 16-byte chunk (4 channels of one pixel), conflict-free thanks to
         // the swizzle.
+        // Stage 1: the group's samples are contiguous in memory ([n][OC][pix]); one round of coalesced
+        // float4 loads brings them into shared memory.
+        const int nfl = rows * OC;  // floats of this group
+        {
+            const float4* src = reinterpret_cast<const float4*>(a.dz_chw + size_t(n0) * OC * pix);
+            for (int i = threadIdx.x; i < nfl / 4; i += kConvThreads) reinterpret_cast<float4*>(stage)[i] = __ldg(src + i);
+            for (int i = (nfl & ~3) + threadIdx.x; i < nfl; i += kConvThreads) stage[i] = __ldg(a.dz_chw + size_t(n0) * OC * pix + i);
+        }
+        __syncthreads();
+        // Stage 2: shared -> shared transpose into the four shifted, swizzled K-major tiles.
         constexpr int kItems = 4 * (OC / 4) * kTileRows;
-        for (int i0 = threadIdx.x; i0 < kItems; i0 += 4 * kConvThreads) {
-            float4 v[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) {  // issue every load of the batch before the first store
-                const int i = i0 + u * kConvThreads;
-                const int r = i % kTileRows, oc4 = (i / kTileRows) % (OC / 4), sft = i / (kTileRows * (OC / 4));
-                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (i < kItems && r < rows) {
-                    const int g = r / pix, p = r % pix;
-                    const int jj = p / a.ow + (sft >> 1), ix = p % a.ow + (sft & 1);
-                    if (jj < a.oh && ix < a.ow) {
-                        const float* src = a.dz_chw + (size_t(n0 + g) * OC + oc4 * 4) * pix + jj * a.ow + ix;
-                        v[u] = make_float4(__ldg(src), __ldg(src + pix), __ldg(src + 2 * pix), __ldg(src + 3 * pix));
-                    }
-                }
+        for (int i = threadIdx.x; i < kItems; i += kConvThreads) {
+            const int r = i % kTileRows, oc4 = (i / kTileRows) % (OC / 4), sft = i / (kTileRows * (OC / 4));
+            if (r >= rows) continue;
+            const int g = r / pix, p = r % pix;
+            const int jj = p / a.ow + (sft >> 1), ix = p % a.ow + (sft & 1);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (jj < a.oh && ix < a.ow) {
+                const float* src = stage + (g * OC + oc4 * 4) * pix + jj * a.ow + ix;
+                v = make_float4(src[0], src[pix], src[2 * pix], src[3 * pix]);
             }
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const int i = i0 + u * kConvThreads;
-                const int r = i % kTileRows, oc4 = (i / kTileRows) % (OC / 4), sft = i / (kTileRows * (OC / 4));
-                if (i < kItems && r < rows)
-                    *reinterpret_cast<float4*>(a_tiles + sft * kATile + r * 128 + ((oc4 ^ (r & 7)) << 4)) = v[u];
-            }
+            *reinterpret_cast<float4*>(a_tiles + sft * kATile + r * 128 + ((oc4 ^ (r & 7)) << 4)) = v;
         }
     } else if (warp == 0) {
         if (lane == 0) {
@@ -386,7 +385,7 @@ int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const 
     if (int rc = encode_tmap_f32(&tm, dz_nhwc, 4, dims, strides, box, nullptr, 128)) return rc;
     ConvBwdArgs a{dz_is_chw ? dz : nullptr, w, a_prev_nhwc, dx_nhwc, s->n, s->oh, s->ow, s->h, s->w, group, act_prev};
     auto kern = tc_conv3x3s2_bwd_data_kernel<32, 16>;
-    constexpr size_t smem = 4 * size_t(kTileRows) * 32 * 4 + kTaps * 16 * 32 * 4 + 1024 + 64;
+    constexpr size_t smem = 4 * size_t(kTileRows) * 32 * 4 + kTaps * 16 * 32 * 4 + size_t(kTileRows) * 32 * 4 + 1024 + 64;
     static bool configured = false;
     if (!configured) {
         B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));

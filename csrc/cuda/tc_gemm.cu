@@ -88,9 +88,11 @@ struct EpiArgs {
                         // (CHW-flattened -> HWC: hands the convolution below its NHWC gradient directly)
 };
 
+constexpr int kMaxSplitK = 4;
 template <int BLOCK_N>
 constexpr size_t smem_bytes() {
-    return size_t(stages_for<BLOCK_N>()) * (kABytes + BLOCK_N * BLOCK_K * 4) + 1024 /*alignment slack*/ + 512 /*barriers*/;
+    return size_t(stages_for<BLOCK_N>()) * (kABytes + BLOCK_N * BLOCK_K * 4) + 1024 /*alignment slack*/ + 512 /*barriers*/ +
+           (BLOCK_N == 16 ? size_t(kMaxSplitK - 1) * BLOCK_M * BLOCK_N * 4 : 0) /*split-K partials of the cluster peers*/;
 }
 
 template <int BLOCK_N, bool A_MN, bool B_MN, int EPI>
@@ -111,10 +113,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint64_t* empty_bar = full_bar + kStages;
     uint64_t* tmem_full_bar = empty_bar + kStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+    float* splitk_red = reinterpret_cast<float*>(smem + kStages * kStageBytes + 512);  // [peers][BLOCK_M][BLOCK_N]
 
     const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
     const int m0 = blockIdx.y * BLOCK_M, n0 = blockIdx.x * BLOCK_N;
-    const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+    // Split-K: gridDim.z CTAs form one cluster; CTA z accumulates k-blocks [kb0, kb1) in its own TMEM, the
+    // peers ship their partial tiles into CTA 0's shared memory (DSMEM), CTA 0 adds them and runs the epilogue.
+    const int splits = int(gridDim.z), zrank = int(blockIdx.z);
+    const int total_kb = (K + BLOCK_K - 1) / BLOCK_K;
+    const int kb0 = total_kb * zrank / splits, kb1 = total_kb * (zrank + 1) / splits;
+    const int num_kb = kb1 - kb0;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_a);
@@ -133,6 +141,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();               // everything above overlapped the previous kernel's tail
     pdl_launch_dependents();  // let the next kernel begin its own prologue
+    float rs = 0.0f;          // bias-gradient partial of an epilogue thread (backward-weight only)
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -144,7 +153,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 uint8_t* a_dst = smem + s * kStageBytes;
                 uint8_t* b_dst = a_dst + kABytes;
                 mbar_arrive_expect_tx(&full_bar[s], kStageBytes);
-                const int k0 = kb * BLOCK_K;
+                const int k0 = (kb0 + kb) * BLOCK_K;
                 if (A_MN) {
 #pragma unroll
                     for (int g = 0; g < BLOCK_M / 32; g++) tma_load_2d(a_dst + g * 4096, &tmap_a, &full_bar[s], m0 + 32 * g, k0);
@@ -189,8 +198,6 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         // ===== epilogue warps =====
         const int q = warp & 3;             // TMEM lane quarter this warp may access
         const int row_in_tile = 32 * q + lane;
-        const int m = m0 + row_in_tile;
-        float rs = 0.0f;
         if (kRowSum) {
             // Bias gradient: column sums of dz == row sums of the staged M-major A tile.  Row r of the
             // tile is one batch sample; this thread owns column `row_in_tile` (undoing the 32-byte-atom swizzle).
@@ -211,6 +218,24 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
+        if (BLOCK_N == 16 && splits > 1) {
+            if (zrank != 0) {
+                float v[16];
+                tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16), v);
+                const uint32_t dst = map_to_cluster_rank(smem_u32(splitk_red + (size_t(zrank - 1) * BLOCK_M + row_in_tile) * BLOCK_N), 0);
+#pragma unroll
+                for (int i = 0; i < 4; i++) st_cluster_f32x4(dst + 16 * i, v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            }
+        }
+    }
+    if (BLOCK_N == 16 && splits > 1) {
+        __syncwarp();
+        cluster_sync_all();  // peers' partial tiles have landed in CTA 0
+    }
+    if (warp >= 2 && zrank == 0) {
+        const int q = warp & 3;
+        const int row_in_tile = 32 * q + lane;
+        const int m = m0 + row_in_tile;
         if (EPI == kEpiSoftmax) {
             // Whole row (<= 16 logits) in this thread: softmax, cross-entropy gradient and the reference's
             // metrics (cnn.c:125-143, :275-286, :508-513) without another kernel or another pass over memory.
@@ -273,6 +298,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             float v[16];
             __syncwarp();  // tcgen05.ld is warp-collective: reconverge after the guarded stores below
             tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(c0), v);
+            if (BLOCK_N == 16 && splits > 1) {
+                for (int pz = 0; pz < splits - 1; pz++) {
+                    const float4* pr = reinterpret_cast<const float4*>(splitk_red + (size_t(pz) * BLOCK_M + row_in_tile) * BLOCK_N);
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const float4 t4 = pr[i];
+                        v[4 * i] += t4.x; v[4 * i + 1] += t4.y; v[4 * i + 2] += t4.z; v[4 * i + 3] += t4.w;
+                    }
+                }
+            }
             const int n_first = n0 + c0;
             if (m < M && n_first < N) {
                 float* crow = ep.C + size_t(m) * ep.ldc + n_first;
@@ -346,7 +381,8 @@ int make_operand_map(CUtensorMap* tm, const float* base, bool mn_major, int rows
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 template <int BLOCK_N, bool A_MN, bool B_MN, int EPI>
-int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const EpiArgs& ep, int M, int N, int K, cudaStream_t st) {
+int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const EpiArgs& ep, int M, int N, int K, cudaStream_t st,
+               int splits = 1) {
     auto kern = tc_gemm_kernel<BLOCK_N, A_MN, B_MN, EPI>;
     constexpr size_t smem = smem_bytes<BLOCK_N>();
     static bool configured = false;
@@ -354,8 +390,9 @@ int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const EpiArgs& ep, 
         B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         configured = true;
     }
-    const dim3 grid(ceil_div(N, BLOCK_N), ceil_div(M, BLOCK_M));
-    B200CNN_CUDA(launch_kernel(kern, grid, dim3(kThreads), smem, st, ta, tb, ep, M, N, K));
+    if (BLOCK_N != 16) splits = 1;
+    const dim3 grid(ceil_div(N, BLOCK_N), ceil_div(M, BLOCK_M), splits);
+    B200CNN_CUDA(launch_kernel_cluster(kern, grid, dim3(kThreads), smem, st, splits, ta, tb, ep, M, N, K));
     return 0;
 }
 
@@ -383,7 +420,13 @@ int dispatch(const float* A, int a_rows, int lda, const float* B, int b_rows, in
         case 64: return launch_cfg<64, A_MN, B_MN, EPI>(ta, tb, ep, M, N, K, st);
         case 32: return launch_cfg<32, A_MN, B_MN, EPI>(ta, tb, ep, M, N, K, st);
         default:
-            if constexpr (!B_MN) return launch_cfg<16, A_MN, B_MN, EPI>(ta, tb, ep, M, N, K, st);
+            if constexpr (!B_MN) {
+                // Long-K, few-CTA forward GEMMs (fc1: K = 1568 on 26 CTAs): 4-way split-K across a cluster.
+                const int total_kb = ceil_div(K, BLOCK_K);
+                const int ctas = ceil_div(N, 16) * ceil_div(M, BLOCK_M);
+                const int splits = (EPI == kEpiBiasAct && total_kb >= 16 && ctas * kMaxSplitK <= 148) ? kMaxSplitK : 1;
+                return launch_cfg<16, A_MN, B_MN, EPI>(ta, tb, ep, M, N, K, st, splits);
+            }
             return set_error(kInvalidValue, "tc_gemm: no tile configuration");
     }
 }

@@ -85,7 +85,8 @@ int b200cnn_conv3x3_fwd_nhwc(const float* x_nhwc, const float* w, const float* b
 int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
                                     float* dx_nhwc, const b200cnn_conv_shape* s, b200cnn_stream stream);
 /* dw (OIHW) / db for NHWC activations: x NHWC (or a 1-channel image, uint8 allowed), dz NHWC or CHW.
- * Register-tiled CUDA-core kernel + fixed-order reduction of per-block partial sums held in `scratch`. */
+ * Register-tiled CUDA-core kernel + fixed-order reduction of per-block partial sums held in `scratch`
+ * (zero the scratch once after allocating it: its last word is a self-resetting completion counter). */
 size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s);
 int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const float* dz, int dz_is_chw, float* dw, float* db,
                                    int accumulate, void* scratch, const b200cnn_conv_shape* s, b200cnn_stream stream);

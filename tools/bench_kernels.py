@@ -40,7 +40,7 @@ w1, b1, a1, dz1 = R(16, 1, 3, 3), R(16), R(B, 14, 14, 16), R(B, 14, 14, 16)
 w2, b2, a2, dz2 = R(32, 16, 3, 3), R(32), R(B, 1568), R(B, 1568)
 dw1, db1, dw2, db2 = R(16, 9), R(16), R(32, 144), R(32)
 a1n, y1 = R(B, 16, 14, 14), R(B, 16, 14, 14)
-scr = torch.empty(max(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(s2)), lib.b200cnn_conv2d_bwd_weight_scratch_bytes(C.byref(s2))), dtype=torch.uint8, device="cuda")
+scr = torch.zeros(max(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(s2)), lib.b200cnn_conv2d_bwd_weight_scratch_bytes(C.byref(s2))), dtype=torch.uint8, device="cuda")
 out["simt.conv1.fwd"] = timeit("simt conv1 fwd (u8 -> NCHW)", lambda: lib.b200cnn_conv2d_fwd(p(x8), 1, p(w1), p(b1), p(y1), C.byref(s1), 2, st))
 out["simt.conv2.fwd"] = timeit("simt conv2 fwd NCHW", lambda: lib.b200cnn_conv2d_fwd(p(a1n), 0, p(w2), p(b2), p(a2), C.byref(s2), 2, st))
 out["tc.conv2.fwd"] = timeit("tc   conv2 fwd NHWC implicit GEMM", lambda: lib.b200cnn_conv3x3_fwd_nhwc(p(a1), p(w2), p(b2), p(a2), 1568, C.byref(s2), 2, st))

@@ -40,7 +40,7 @@ for n in (2, 256, 7):
     stat(f"bwd_data(chw dz) n{n} rc={rc}", dx2.permute(0, 3, 1, 2), want)
     # backward-weight, NHWC x + CHW / NHWC dz
     nbytes = lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp))
-    scratch = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    scratch = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
     dzm = dz * 1.0
     wr = w.clone().requires_grad_(); a1r = a1.clone()
     y = F.conv2d(a1r, wr, None, 2, 1); y.backward(dzm)
@@ -55,7 +55,7 @@ for n in (2, 256, 7):
     shp1 = N.ConvShape(n, 1, 28, 28, 16, 14, 14, 3, 1, 2)
     w1 = torch.zeros(16, 1, 3, 3, device="cuda", requires_grad=True)
     F.conv2d(x8.float() / 255.0, w1, None, 2, 1).backward(dz1)
-    scratch = torch.empty(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp1)), dtype=torch.uint8, device="cuda")
+    scratch = torch.zeros(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp1)), dtype=torch.uint8, device="cuda")
     dw1 = torch.full((16, 1, 3, 3), 7.0, device="cuda"); db1 = torch.full((16,), 7.0, device="cuda")
     rc = lib.b200cnn_conv2d_bwd_weight_nhwc(p(x8), 1, p(dz1_nhwc), 0, p(dw1), p(db1), 0, p(scratch), C.byref(shp1), st)
     stat(f"bwd_weight c1 u8 n{n} rc={rc}", dw1, w1.grad)
