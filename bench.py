@@ -167,27 +167,58 @@ def run_b200(args):
         host_y = torch.empty((pool, BATCH), dtype=torch.uint8).pin_memory()
         host_x.copy_(data_x[: pool * BATCH].reshape(pool, BATCH, 784).cpu())
         host_y.copy_(data_y[: pool * BATCH].reshape(pool, BATCH).cpu())
-        loss_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+        # Two pinned result slots: the host reads step i-1's loss while step i runs (each step's inputs are still
+        # copied from pinned host memory and each step's loss is still read back inside the timed region).
+        loss_host = [torch.zeros(4, dtype=torch.float32).pin_memory() for _ in range(2)]
+        loss_ready = [torch.cuda.Event(), torch.cuda.Event()]
         metrics = engine.metrics_tensor()
         losses = []
 
-        def e2e_step(i):
-            xs.copy_(host_x[i % pool], non_blocking=True)
-            ys.copy_(host_y[i % pool], non_blocking=True)
-            step(xs, ys)
-            loss_host.copy_(metrics, non_blocking=True)
-            stream.synchronize()  # the caller looks at the loss of THIS step before issuing the next
-            return float(loss_host[0])
+        # Double-buffered device staging: batch i+1 crosses PCIe on the copy stream while batch i trains.
+        stage = [(xs, ys), (torch.empty_like(xs), torch.empty_like(ys))]
+        copy_stream = torch.cuda.Stream(device=device)
+        copied = [torch.cuda.Event(), torch.cuda.Event()]
+        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        for ev in consumed:
+            ev.record(stream)
+
+        def e2e_upload(i):
+            sx, sy = stage[i % 2]
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(consumed[i % 2])  # the step that last read this buffer has finished
+                sx.copy_(host_x[i % pool], non_blocking=True)
+                sy.copy_(host_y[i % pool], non_blocking=True)
+                copied[i % 2].record(copy_stream)
+
+        def e2e_enqueue(i):
+            sx, sy = stage[i % 2]
+            stream.wait_event(copied[i % 2])
+            step(sx, sy)
+            consumed[i % 2].record(stream)
+            loss_host[i % 2].copy_(metrics, non_blocking=True)
+            loss_ready[i % 2].record(stream)
+
+        def e2e_collect(i):
+            loss_ready[i % 2].synchronize()
+            return float(loss_host[i % 2][0])
 
         for i in range(W):
-            e2e_step(i)
+            e2e_upload(i)
+            e2e_enqueue(i)
+            e2e_collect(i)
         barrier()
         engine.reset_metrics()
         stream.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
+        e2e_upload(0)
         for i in range(K):
-            losses.append(e2e_step(W + i))
+            if i + 1 < K:
+                e2e_upload(i + 1)
+            e2e_enqueue(i)
+            if i > 0:
+                losses.append(e2e_collect(i - 1))
+        losses.append(e2e_collect(K - 1))
         e1.record(stream)
         stream.synchronize()
         barrier()

@@ -55,12 +55,19 @@ struct b200cnn_engine {
     const void* last_images = nullptr;
     int last_is_u8 = 0;
     int last_batch = 0;
-    // graph cache (one entry: the training loop reuses the same staging buffers every step)
-    cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};  // one per gradient-buffer parity
-    const void* g_images = nullptr;
-    const uint8_t* g_labels = nullptr;
-    int g_batch = 0, g_is_u8 = 0;
-    cudaStream_t g_stream = nullptr;
+    // Graph cache: a few entries, so a caller can rotate between staging buffers (copy batch i+1 while batch i
+    // trains).  Key = (buffers, batch, input type, stream, backend); one executable per gradient-buffer parity.
+    struct GraphEntry {
+        cudaGraphExec_t exec[2] = {nullptr, nullptr};
+        const void* images = nullptr;
+        const uint8_t* labels = nullptr;
+        int batch = 0, is_u8 = 0, backend = -1;
+        cudaStream_t stream = nullptr;
+        unsigned long last_use = 0;
+    };
+    static constexpr int kGraphEntries = 4;
+    GraphEntry graphs[kGraphEntries];
+    unsigned long graph_clock = 0;
     b200cnn_comm* comm = nullptr;
     int launches_per_step = 0;
     cudaStream_t side = nullptr;          // weight-gradient kernels run here, next to the data-gradient chain
@@ -70,7 +77,6 @@ struct b200cnn_engine {
     long bucket_lo = -1, bucket_hi = -1;
     bool last_fast = false;   // layout of layer 1's activations in the last forward (NHWC when true)
     bool fast_chain = false;  // conv(C_in=1) -> tc conv3x3 -> FC pattern: NHWC activations + tcgen05 convolutions
-    int g_backend = -1;
 };
 
 namespace {
@@ -384,8 +390,9 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
 
 extern "C" void b200cnn_engine_destroy(b200cnn_engine* e) {
     if (!e) return;
-    for (cudaGraphExec_t g : e->graph_exec)
-        if (g) cudaGraphExecDestroy(g);
+    for (auto& ge : e->graphs)
+        for (cudaGraphExec_t g : ge.exec)
+            if (g) cudaGraphExecDestroy(g);
     if (e->own_buffers) {
         cudaFree(e->params);
         cudaFree(e->grads);
@@ -522,16 +529,30 @@ extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, 
         e->launches_per_step = launches;
         return rc;
     }
-    const bool same_key = e->g_images == images && e->g_labels == labels && e->g_batch == batch &&
-                          e->g_is_u8 == x_is_u8 && e->g_stream == st && e->g_backend == current_backend();
-    if (!same_key) {
-        for (cudaGraphExec_t& g : e->graph_exec)
+    // find (or make room for) the cache entry of this key
+    b200cnn_engine::GraphEntry* ge = nullptr;
+    for (auto& c : e->graphs)
+        if (c.images == images && c.labels == labels && c.batch == batch && c.is_u8 == x_is_u8 && c.stream == st &&
+            c.backend == current_backend() && (c.exec[0] || c.exec[1]))
+            ge = &c;
+    if (!ge) {
+        ge = &e->graphs[0];
+        for (auto& c : e->graphs)
+            if (c.last_use < ge->last_use) ge = &c;  // least recently used
+        for (cudaGraphExec_t& g : ge->exec)
             if (g) {
                 cudaGraphExecDestroy(g);
                 g = nullptr;
             }
+        ge->images = images;
+        ge->labels = labels;
+        ge->batch = batch;
+        ge->is_u8 = x_is_u8;
+        ge->stream = st;
+        ge->backend = current_backend();
     }
-    if (!e->graph_exec[par]) {
+    ge->last_use = ++e->graph_clock;
+    if (!ge->exec[par]) {
         if (st == nullptr) return set_error(kInvalidValue, "engine_train_step: graph capture needs a non-default stream");
         cudaGraph_t graph = nullptr;
         B200CNN_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
@@ -543,18 +564,12 @@ extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, 
             return rc;
         }
         if (ce != cudaSuccess) return set_error(int(ce), "engine_train_step: capture failed: %s", cudaGetErrorString(ce));
-        const cudaError_t ie = cudaGraphInstantiate(&e->graph_exec[par], graph, 0);
+        const cudaError_t ie = cudaGraphInstantiate(&ge->exec[par], graph, 0);
         cudaGraphDestroy(graph);
         if (ie != cudaSuccess) return set_error(int(ie), "engine_train_step: instantiate failed: %s", cudaGetErrorString(ie));
-        e->g_images = images;
-        e->g_labels = labels;
-        e->g_batch = batch;
-        e->g_is_u8 = x_is_u8;
-        e->g_stream = st;
-        e->g_backend = current_backend();
         e->launches_per_step = launches;
     }
-    B200CNN_CUDA(cudaGraphLaunch(e->graph_exec[par], st));
+    B200CNN_CUDA(cudaGraphLaunch(ge->exec[par], st));
     return 0;
 }
 
@@ -590,11 +605,12 @@ extern "C" int b200cnn_engine_launches_per_step(const b200cnn_engine* e) { retur
 // Data-parallel hook (declared in comm.cuh): the communicator must have been created over this
 // engine's bound parameter / gradient buffers.
 extern "C" int b200cnn_engine_attach_comm(b200cnn_engine* e, b200cnn_comm* comm) {
-    for (cudaGraphExec_t& g : e->graph_exec)
-        if (g) {
-            cudaGraphExecDestroy(g);
-            g = nullptr;
-        }
+    for (auto& ge : e->graphs)
+        for (cudaGraphExec_t& g : ge.exec)
+            if (g) {
+                cudaGraphExecDestroy(g);
+                g = nullptr;
+            }
     if (!comm) {
         e->comm = nullptr;
         return 0;
