@@ -6,6 +6,8 @@
 //   * the first convolution's backward-weight (1 input channel, 144 weights).
 // Both write per-block partial sums that conv2d_bwd_weight_reduce sums in a fixed order.
 // Replaces the weight half of Layer_feedBack_conv (/root/reference/cnn.c:236, :242).
+#include <algorithm>
+
 #include "backend.cuh"
 #include "common.cuh"
 
@@ -40,7 +42,7 @@ conv_bwd_weight_nhwc_kernel(const float* __restrict__ x, const float* __restrict
     const bool worker = t < nthr_work;
     const int oc4 = t % oc4n, c4 = (t / oc4n) % c4n, tap = t / (oc4n * c4n);
     const int ky = tap / s.k, kx = tap % s.k;
-    const bool bias_thread = worker && tap == 0 && c4 == 0;
+    const bool bias_thread = worker && c4 == 0;  // the kk tap-threads of each oc4 share the bias sum (pixel p = tap mod kk)
 
     const int n0 = blockIdx.x * spb, ns = min(spb, s.n - n0);
     pdl_wait();
@@ -54,15 +56,20 @@ conv_bwd_weight_nhwc_kernel(const float* __restrict__ x, const float* __restrict
             const float4* gg = reinterpret_cast<const float4*>(dz + size_t(n0) * out_sz);
             for (int i = t; i < ns * out_sz / 4; i += blockDim.x) reinterpret_cast<float4*>(gs)[i] = __ldg(gg + i);
         } else {
-            // CHW -> HWC while staging: coalesced reads along the pixel index.
+            // CHW -> HWC while staging: coalesced reads along the pixel index; (p, oc, nn) advance incrementally
+            // instead of three runtime divisions per element.
+            int p = t % pix, oc = (t / pix) % OC, nn = t / out_sz;
+            const int dp = int(blockDim.x) % pix, doc = int(blockDim.x) / pix;
             for (int i = t; i < ns * out_sz; i += blockDim.x) {
-                const int p = i % pix, oc = (i / pix) % OC, nn = i / out_sz;
                 gs[(nn * pix + p) * OC + oc] = __ldg(dz + size_t(n0) * out_sz + i);
+                p += dp;
+                oc += doc;
+                if (p >= pix) { p -= pix; oc++; }
+                while (oc >= OC) { oc -= OC; nn++; }
             }
         }
     }
     __syncthreads();
-    if (!worker) return;
 
     float acc[4][4];
     float bacc[4] = {0.f, 0.f, 0.f, 0.f};
@@ -74,11 +81,11 @@ conv_bwd_weight_nhwc_kernel(const float* __restrict__ x, const float* __restrict
     tap_range(ky, s.stride, s.pad, s.h, s.oh, oy0, oy1);
     tap_range(kx, s.stride, s.pad, s.w, s.ow, ox0, ox1);
 
-    for (int nn = 0; nn < ns; nn++) {
+    for (int nn = 0; worker && nn < ns; nn++) {
         const float* xsn = xs + nn * in_sz;
         const float* gsn = gs + nn * out_sz;
         if (bias_thread)
-            for (int p = 0; p < pix; p++) {
+            for (int p = tap; p < pix; p += kk) {
                 const float4 g = *reinterpret_cast<const float4*>(gsn + p * OC + oc4 * 4);
                 bacc[0] += g.x; bacc[1] += g.y; bacc[2] += g.z; bacc[3] += g.w;
             }
@@ -102,72 +109,105 @@ conv_bwd_weight_nhwc_kernel(const float* __restrict__ x, const float* __restrict
     }
     const int nw = OC * C * kk, nout = nw + OC;
     float* out = partials + size_t(blockIdx.x) * nout;
+    if (worker) {
 #pragma unroll
-    for (int i = 0; i < 4; i++)
+        for (int i = 0; i < 4; i++)
 #pragma unroll
-        for (int j = 0; j < 4; j++) out[((oc4 * 4 + i) * C + c4 * 4 + j) * kk + tap] = acc[i][j];  // OIHW
+            for (int j = 0; j < 4; j++) out[((oc4 * 4 + i) * C + c4 * 4 + j) * kk + tap] = acc[i][j];  // OIHW
+    }
+    // bias: the kk tap-threads of an oc4 group add their pixel slices in tap order through shared memory
+    __syncthreads();  // every worker is past its reads of xs / gs: reuse the front of xs
+    float* bred = xs;  // [kk][OC]
     if (bias_thread)
 #pragma unroll
-        for (int i = 0; i < 4; i++) out[nw + oc4 * 4 + i] = bacc[i];
+        for (int i = 0; i < 4; i++) bred[tap * OC + oc4 * 4 + i] = bacc[i];
+    __syncthreads();
+    if (t < OC) {
+        float a = 0.f;
+        for (int k2 = 0; k2 < kk; k2++) a += bred[k2 * OC + t];
+        out[nw + t] = a;
+    }
 }
 
 // Single input channel: x [n][h][w] (uint8 or float), dz NHWC [n][oh][ow][OC].
-// thread = (oc, tap, pixel-row slice): kSlices threads share one output and are summed through shared memory.
-constexpr int kC1Slices = 4;
+// Work item = (4 output channels, 1 tap) or (4 output channels of the bias); kC1Threads / items pixel-row slices
+// work on each item and are summed through shared memory.  Inner loop: one float4 of dz + one pixel -> 4 FMAs.
+constexpr int kC1Threads = 640;
 
 template <typename TIn>
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(kC1Threads)
 conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restrict__ dz, float* __restrict__ partials,
                                b200cnn_conv_shape s, int spb, float in_scale, float* __restrict__ dw, float* __restrict__ db,
                                int accumulate, unsigned* __restrict__ counter) {
     extern __shared__ __align__(16) float sm[];
-    const int OC = s.oc, kk = s.k * s.k, pix = s.oh * s.ow;
+    const int OC = s.oc, kk = s.k * s.k, pix = s.oh * s.ow, oc4n = OC / 4;
     const int in_sz = s.h * s.w, in_pad = (in_sz + 3) & ~3, out_sz = pix * OC;
     const int t = threadIdx.x;
     const int nw = OC * kk, nout = nw + OC;
+    const int items = oc4n * (kk + 1), slices = kC1Threads / items;
     const int n0 = blockIdx.x * spb, ns = min(spb, s.n - n0);
     float* xs = sm;                         // [ns][in_pad]
     float* gs = sm + size_t(spb) * in_pad;  // [ns][pix][OC]
-    float* red = gs + size_t(spb) * out_sz; // [kC1Slices][nout]
+    float* red = gs + size_t(spb) * out_sz; // [slices][nout]
     pdl_wait();
     pdl_launch_dependents();
-    for (int i = t; i < ns * in_sz; i += blockDim.x)
-        xs[(i / in_sz) * in_pad + i % in_sz] = cvt_in<TIn>(__ldg(x + size_t(n0) * in_sz + i), in_scale);
+    if (sizeof(TIn) == 1 && (in_sz & 3) == 0) {
+        // four pixels per load
+        const uchar4* x4 = reinterpret_cast<const uchar4*>(x + size_t(n0) * in_sz);
+        for (int i = t; i < ns * in_sz / 4; i += kC1Threads) {
+            const uchar4 v = __ldg(x4 + i);
+            const int nn = (4 * i) / in_sz, off = (4 * i) % in_sz;
+            float* d = xs + nn * in_pad + off;
+            d[0] = v.x * in_scale; d[1] = v.y * in_scale; d[2] = v.z * in_scale; d[3] = v.w * in_scale;
+        }
+    } else {
+        for (int i = t; i < ns * in_sz; i += kC1Threads)
+            xs[(i / in_sz) * in_pad + i % in_sz] = cvt_in<TIn>(__ldg(x + size_t(n0) * in_sz + i), in_scale);
+    }
     {
         const float4* gg = reinterpret_cast<const float4*>(dz + size_t(n0) * out_sz);
-        for (int i = t; i < ns * out_sz / 4; i += blockDim.x) reinterpret_cast<float4*>(gs)[i] = __ldg(gg + i);
+        for (int i = t; i < ns * out_sz / 4; i += kC1Threads) reinterpret_cast<float4*>(gs)[i] = __ldg(gg + i);
     }
     __syncthreads();
-    const int o = t % nout, slice = t / nout;  // blockDim = nout * kC1Slices (rounded up to a warp)
-    if (slice < kC1Slices) {
-        float acc = 0.f;
-        if (o < nw) {
-            const int oc = o % OC, tap = o / OC;
+    const int item = t % items, slice = t / items;
+    if (slice < slices) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        const int oc4 = item % oc4n, tap = item / oc4n;  // tap == kk: the bias item
+        if (tap < kk) {
             const int ky = tap / s.k, kx = tap % s.k;
             int oy0, oy1, ox0, ox1;
             tap_range(ky, s.stride, s.pad, s.h, s.oh, oy0, oy1);
             tap_range(kx, s.stride, s.pad, s.w, s.ow, ox0, ox1);
-            for (int nn = 0; nn < ns; nn++)
-                for (int oy = oy0 + slice; oy < oy1; oy += kC1Slices) {
-                    const float* xrow = xs + nn * in_pad + (oy * s.stride - s.pad + ky) * s.w - s.pad + kx;
-                    const float* grow = gs + (nn * pix + oy * s.ow) * OC + oc;
-#pragma unroll 7
-                    for (int ox = ox0; ox < ox1; ox++) acc = fmaf(grow[ox * OC], xrow[ox * s.stride], acc);
+            const int nrows = oy1 - oy0;
+            for (int rr = slice; rr < ns * nrows; rr += slices) {
+                const int nn = rr / nrows, oy = oy0 + rr % nrows;
+                const float* xp = xs + nn * in_pad + (oy * s.stride - s.pad + ky) * s.w - s.pad + kx + ox0 * s.stride;
+                const float4* gp = reinterpret_cast<const float4*>(gs + (nn * pix + oy * s.ow + ox0) * OC) + oc4;
+                for (int ox = ox0; ox < ox1; ox++, xp += s.stride, gp += oc4n) {
+                    const float4 g = *gp;
+                    const float xv = *xp;
+                    acc[0] = fmaf(g.x, xv, acc[0]);
+                    acc[1] = fmaf(g.y, xv, acc[1]);
+                    acc[2] = fmaf(g.z, xv, acc[2]);
+                    acc[3] = fmaf(g.w, xv, acc[3]);
                 }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) red[slice * nout + (oc4 * 4 + i) * kk + tap] = acc[i];  // OIHW, 1 input channel
         } else {
-            for (int nn = 0; nn < ns; nn++)
-                for (int p = slice; p < pix; p += kC1Slices) acc += gs[(nn * pix + p) * OC + (o - nw)];
+            for (int p = slice; p < ns * pix; p += slices) {
+                const float4 g = *(reinterpret_cast<const float4*>(gs + p * OC) + oc4);
+                acc[0] += g.x; acc[1] += g.y; acc[2] += g.z; acc[3] += g.w;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) red[slice * nout + nw + oc4 * 4 + i] = acc[i];
         }
-        red[slice * nout + o] = acc;
     }
     __syncthreads();
     if (t < nout) {
-        float a = red[t];
-#pragma unroll
-        for (int sl = 1; sl < kC1Slices; sl++) a += red[sl * nout + t];
-        // OIHW with one input channel: index oc*kk + tap; bias after the weights.
-        const int oc = t % OC, tap = t / OC;
-        partials[size_t(blockIdx.x) * nout + (t < nw ? oc * kk + tap : t)] = a;
+        float a = 0.f;
+        for (int sl = 0; sl < slices; sl++) a += red[sl * nout + t];
+        partials[size_t(blockIdx.x) * nout + t] = a;
     }
     // The block that finishes last sums all partials in block order (fixed order => reproducible) and
     // writes the gradient: no second kernel on the tail of the backward pass.
@@ -181,17 +221,25 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
     __syncthreads();
     if (!is_last) return;
     __threadfence();
-    const int j = t % nout, part = t / nout;  // kC1Slices threads per output again
-    if (part < kC1Slices) {
+    const int j = t % nout, part = t / nout, parts = kC1Threads / nout;
+    if (part < parts) {
+        // 8 independent L2 loads in flight per thread (a serial load-add chain would cost ~0.35 us per partial).
         float a = 0.f;
-        for (int c = part; c < int(gridDim.x); c += kC1Slices) a += __ldcg(partials + size_t(c) * nout + j);
+        int c = part;
+        for (; c + 7 * parts < int(gridDim.x); c += 8 * parts) {
+            float v[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) v[u] = __ldcg(partials + size_t(c + u * parts) * nout + j);
+#pragma unroll
+            for (int u = 0; u < 8; u++) a += v[u];
+        }
+        for (; c < int(gridDim.x); c += parts) a += __ldcg(partials + size_t(c) * nout + j);
         red[part * nout + j] = a;
     }
     __syncthreads();
     if (t < nout) {
         float a = red[t];
-#pragma unroll
-        for (int sl = 1; sl < kC1Slices; sl++) a += red[sl * nout + t];
+        for (int sl = 1; sl < parts; sl++) a += red[sl * nout + t];
         float* dst = t < nw ? (dw ? dw + t : nullptr) : (db ? db + (t - nw) : nullptr);
         if (dst) *dst = accumulate ? *dst + a : a;
     }
@@ -203,7 +251,7 @@ int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks
                          cudaStream_t st);
 
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8) {
-    if (s->c == 1) return s->oc * s->k * s->k + s->oc <= 512 && s->oc % 4 == 0;
+    if (s->c == 1) return s->oc * s->k * s->k + s->oc <= kC1Threads && s->oc % 4 == 0;
     return !x_is_u8 && s->c % 4 == 0 && s->oc % 4 == 0 && (s->oc / 4) * (s->c / 4) * s->k * s->k <= 512;
 }
 
@@ -228,17 +276,18 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
     if (s->c == 1) {
         if (dz_chw) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: CHW gradients are only read by the multi-channel kernel");
         const int nout = nw + s->oc;
-        const int threads = ((nout * kC1Slices + 31) / 32) * 32;
-        // completion counter: the last 128 bytes of the partials area (zero at allocation, self-resetting)
+        const int items = (s->oc / 4) * (kk + 1);
+        if (items > kC1Threads || nout > kC1Threads) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: layer too large for the single-channel kernel");
+        const int slices = kC1Threads / items;
         unsigned* counter = counter_in ? counter_in : reinterpret_cast<unsigned*>(partials + size_t(chunks) * nout);
-        const size_t smem = (size_t(spb) * (((s->h * s->w + 3) & ~3) + size_t(s->oh) * s->ow * s->oc) + size_t(kC1Slices) * nout) * sizeof(float);
-        if (threads > 1024 || smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: layer too large for the single-channel kernel");
+        const size_t smem = (size_t(spb) * (((s->h * s->w + 3) & ~3) + size_t(s->oh) * s->ow * s->oc) + size_t(std::max(slices, kC1Threads / nout)) * nout) * sizeof(float);
+        if (smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: samples do not fit shared memory");
         if (x_is_u8) {
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, dim3(chunks), dim3(threads), smem, st, static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f, dw, db, accumulate, counter));
+            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, dim3(chunks), dim3(kC1Threads), smem, st, static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f, dw, db, accumulate, counter));
         } else {
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f, dw, db, accumulate, counter));
+            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(kC1Threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f, dw, db, accumulate, counter));
         }
     } else {
         const int work = (s->oc / 4) * (s->c / 4) * kk;

@@ -209,18 +209,33 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
         }
         __syncthreads();
         // Stage 2: shared -> shared transpose into the four shifted, swizzled K-major tiles.
-        constexpr int kItems = 4 * (OC / 4) * kTileRows;
-        for (int i = threadIdx.x; i < kItems; i += kConvThreads) {
-            const int r = i % kTileRows, oc4 = (i / kTileRows) % (OC / 4), sft = i / (kTileRows * (OC / 4));
-            if (r >= rows) continue;
-            const int g = r / pix, p = r % pix;
-            const int jj = p / a.ow + (sft >> 1), ix = p % a.ow + (sft & 1);
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (jj < a.oh && ix < a.ow) {
-                const float* src = stage + (g * OC + oc4 * 4) * pix + jj * a.ow + ix;
-                v = make_float4(src[0], src[pix], src[2 * pix], src[3 * pix]);
+        // Thread r < 128 owns tile row r (one output pixel): its (sample, y, x) is computed once, the loop over
+        // (shift, channel group) has no divisions.  Threads 128..191 take the second half of the channel groups.
+        {
+            const int r = threadIdx.x % kTileRows, half = threadIdx.x / kTileRows;  // half in {0, 1}
+            if (r < rows) {
+                const int g = r / pix, p = r % pix, j = p / a.ow, i = p % a.ow;
+                const float* base = stage + g * OC * pix;
+                const bool two = kConvThreads >= 2 * kTileRows;  // false: 192 threads => rows 0..63 get a helper
+                (void)two;
+                for (int sft = 0; sft < 4; sft++) {
+                    const int jj = j + (sft >> 1), ix = i + (sft & 1);
+                    const bool inb = jj < a.oh && ix < a.ow;
+                    const float* src = base + jj * a.ow + ix;
+                    uint8_t* dst = a_tiles + sft * kATile + r * 128;
+                    // rows 0..63 have two threads (r and r + 128): split the 8 channel groups between them
+                    const int lo = (r < kConvThreads - kTileRows) ? half * (OC / 8) : 0;
+                    const int hi = (r < kConvThreads - kTileRows) ? lo + OC / 8 : (half == 0 ? OC / 4 : 0);
+                    for (int oc4 = lo; oc4 < hi; oc4++) {
+                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (inb) {
+                            const float* s4 = src + oc4 * 4 * pix;
+                            v = make_float4(s4[0], s4[pix], s4[2 * pix], s4[3 * pix]);
+                        }
+                        *reinterpret_cast<float4*>(dst + ((oc4 ^ (r & 7)) << 4)) = v;
+                    }
+                }
             }
-            *reinterpret_cast<float4*>(a_tiles + sft * kATile + r * 128 + ((oc4 ^ (r & 7)) << 4)) = v;
         }
     } else if (warp == 0) {
         if (lane == 0) {
