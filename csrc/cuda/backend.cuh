@@ -34,6 +34,12 @@ int tc_linear_bwd_data_permuted(const float* dz, const float* w, const float* a_
 int tc_linear_bwd_weight(const float* dz, const float* x, float* dw, float* db, int accumulate, int m, int n, int k,
                          int lddz, cudaStream_t st);
 
+// tc_head.cu: fc(tanh) -> fc(softmax) forward + loss + both backward-data GEMMs in one kernel
+bool tc_head_supported(int m, int n1, int n2, int nc, int ldc);
+int tc_head(const float* h1, const float* w2, const float* b2, const float* w3, const float* b3, const uint8_t* labels, float* h2,
+            float* probs, float* dz3, float* dz2, float* dz1, float* metrics, int m, int n1, int n2, int nc, int ldc,
+            cudaStream_t st);
+
 // tc_conv.cu: implicit-GEMM 3x3 convolutions on NHWC activations
 bool tc_conv3x3_fwd_supported(const b200cnn_conv_shape* s);
 int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s,

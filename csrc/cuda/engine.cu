@@ -9,6 +9,7 @@
 // starting on a 128-byte boundary.  The single-GPU update is one kernel over the flat buffer; the
 // data-parallel path binds NVLink-mapped symmetric buffers (b200cnn_engine_bind_buffers) and runs the
 // fused all-reduce + SGD kernel per layer slice instead.
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -103,12 +104,30 @@ b200cnn_conv_shape conv_shape(const EngineLayer& prev, const EngineLayer& l, int
 // to the CUDA-core kernels.
 bool use_fast_chain(const b200cnn_engine* e) { return e->fast_chain && current_backend() != B200CNN_BACKEND_SIMT; }
 
+// True when the last three layers are FC(tanh) -> FC(tanh) -> FC(softmax) of sizes the fused head kernel takes.
+bool use_head(const b200cnn_engine* e, int batch) {
+    // Measured on B200 at batch 256: the fused kernel (2 CTAs, four serial GEMM phases, all epilogue traffic on two
+    // SMs) takes 45 us against 26 us for the five separate kernels it replaces (13-26 CTAs each), so it is opt-in.
+    static const bool enabled = [] {
+        const char* v = getenv("B200CNN_HEAD");
+        return v && v[0] == '1';
+    }();
+    if (!enabled) return false;
+    const auto& L = e->layers;
+    const size_t n = L.size();
+    if (n < 4 || current_backend() == B200CNN_BACKEND_SIMT) return false;
+    for (size_t i = n - 3; i < n; i++)
+        if (L[i].d.type != B200CNN_LAYER_FULL) return false;
+    return tc_head_supported(batch, L[n - 3].nnodes, L[n - 2].nnodes, L[n - 1].nnodes, L[n - 1].ld);
+}
+
+// Forward through layers [1, stop).
 int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
-                    cudaStream_t st, int* launches) {
+                    cudaStream_t st, int* launches, size_t stop = ~size_t(0)) {
     auto& L = e->layers;
     const bool fast = use_fast_chain(e);
     e->last_fast = fast;
-    for (size_t li = 1; li < L.size(); li++) {
+    for (size_t li = 1; li < L.size() && li < stop; li++) {
         EngineLayer& l = L[li];
         const EngineLayer& p = L[li - 1];
         const void* in = (li == 1) ? images : static_cast<const void*>(p.a);
@@ -184,7 +203,8 @@ int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, bool last, cudaSt
 //     wait(dz ready) -> dW/db kernel(s) -> wait(this layer's data gradient issued) -> fused update hook
 // The hook must come after the data-gradient kernel because a two-shot / NVLS update may overwrite the
 // layer's weights on this GPU from a peer.
-int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch, cudaStream_t st, int* launches) {
+int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch, cudaStream_t st, int* launches,
+                     bool head_done = false) {
     auto& L = e->layers;
     float* grads = cur_grads(e);
     const bool fast = use_fast_chain(e);
@@ -226,8 +246,9 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
         }
         if (rc) return rc;
 
-        // Data gradient for the layer below (critical path).
-        if (li > 1) {
+        // Data gradient for the layer below (critical path); the fused head kernel has already produced it for
+        // the last two layers.
+        if (li > 1 && !(head_done && li + 2 >= L.size())) {
             if (l.d.type == B200CNN_LAYER_FULL) {
                 rc = b200cnn_linear_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, batch, l.nnodes, p.nnodes, l.ld, st);
             } else {
@@ -504,8 +525,21 @@ extern "C" int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream st
 
 static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
                         cudaStream_t st, int* launches) {
-    if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches)) return rc;
-    if (int rc = enqueue_backward(e, images, is_u8, batch, st, launches)) return rc;
+    const bool head = use_head(e, batch);
+    if (!head) {
+        if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches)) return rc;
+    } else {
+        // layers below the head, then ONE kernel for fc -> softmax/loss -> both backward-data GEMMs
+        auto& L = e->layers;
+        const size_t n = L.size();
+        if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches, n - 2)) return rc;
+        EngineLayer &l1 = L[n - 3], &l2 = L[n - 2], &l3 = L[n - 1];
+        if (int rc = tc_head(l1.a, e->params + l2.w_off, e->params + l2.b_off, e->params + l3.w_off, e->params + l3.b_off, labels, l2.a,
+                             l3.a, l3.dz, l2.dz, l1.dz, e->metrics, batch, l1.nnodes, l2.nnodes, l3.nnodes, l3.ld, st))
+            return rc;
+        if (launches) (*launches)++;
+    }
+    if (int rc = enqueue_backward(e, images, is_u8, batch, st, launches, head)) return rc;
     return enqueue_update(e, st, launches);
 }
 

@@ -50,6 +50,13 @@ extern "C" int b200cnn_linear_softmax_xent(const float* x, const float* w, const
     return b200cnn_softmax_xent(probs, labels, probs, labels ? dz : nullptr, labels ? metrics : nullptr, m, n, ld, stream);
 }
 
+extern "C" int b200cnn_mlp_head(const float* h1, const float* w2, const float* b2, const float* w3, const float* b3,
+                                const uint8_t* labels, float* h2, float* probs, float* dz3, float* dz2, float* dz1, float* metrics,
+                                int m, int n1, int n2, int nc, int ldc, b200cnn_stream stream) {
+    if (!tc_head_supported(m, n1, n2, nc, ldc)) return set_error(kInvalidValue, "mlp_head: need 16 <= n1, n2 <= 208 (multiples of 4), nc <= ldc <= 16");
+    return tc_head(h1, w2, b2, w3, b3, labels, h2, probs, dz3, dz2, dz1, metrics, m, n1, n2, nc, ldc, as_stream(stream));
+}
+
 // ---- NHWC tensor-core convolution entry points (see include/b200cnn.h) ------------------------------
 extern "C" int b200cnn_conv3x3_fwd_nhwc(const float* x_nhwc, const float* w, const float* b, float* y, int ldy,
                                         const b200cnn_conv_shape* s, int act, b200cnn_stream stream) {

@@ -117,6 +117,15 @@ int b200cnn_softmax_xent(const float* logits, const uint8_t* labels, float* prob
 int b200cnn_linear_softmax_xent(const float* x, const float* w, const float* b, const uint8_t* labels, float* probs,
                                 float* dz, float* metrics, int m, int n, int k, int ld, b200cnn_stream stream);
 
+/* The last two layers of a step fused into one tcgen05 kernel (training only):
+ *   h2 = tanh(h1 W2^T + b2); probs = softmax(h2 W3^T + b3); dz3 = probs - onehot; metrics;
+ *   dz2 = (dz3 W3) * (1 - h2^2); dz1 = (dz2 W2) * (1 - h1^2).
+ * Intermediate operands stay in shared memory / TMEM; h2, dz3, dz2 are also written to global memory for the
+ * weight-gradient kernels.  16 <= n1, n2 <= 208 (multiples of 4), nc <= ldc <= 16. */
+int b200cnn_mlp_head(const float* h1, const float* w2, const float* b2, const float* w3, const float* b3, const uint8_t* labels,
+                     float* h2, float* probs, float* dz3, float* dz2, float* dz1, float* metrics, int m, int n1, int n2, int nc,
+                     int ldc, b200cnn_stream stream);
+
 /* ---- max pooling (K7; not in the reference) ------------------------------------------------ */
 int b200cnn_maxpool_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride,
                         b200cnn_stream stream);

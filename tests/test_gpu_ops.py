@@ -217,3 +217,35 @@ def test_synthetic_and_gather():
     for i in range(0, 64, 7):
         match = (x[128:256] == bx[i]).all(1).nonzero()
         assert match.numel() >= 1 and int(y[128 + int(match[0])]) == int(by[i])
+
+
+@pytest.mark.parametrize("shape", [(256, 200, 200, 10), (100, 64, 128, 7), (300, 208, 36, 16), (1, 16, 16, 2)])
+def test_fused_head_kernel(shape):
+    """fc(tanh) -> fc(softmax) + loss gradient + both backward-data GEMMs in one tcgen05 kernel vs PyTorch."""
+    import ctypes as C
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    m, n1, n2, nc = shape
+    torch.backends.cuda.matmul.allow_tf32 = False
+    h1 = torch.tanh(torch.randn(m, n1, device="cuda"))
+    w2, b2 = torch.randn(n2, n1, device="cuda") / n1 ** 0.5, 0.1 * torch.randn(n2, device="cuda")
+    w3, b3 = torch.randn(nc, n2, device="cuda") / n2 ** 0.5, 0.1 * torch.randn(nc, device="cuda")
+    lab = torch.randint(0, nc, (m,), device="cuda", dtype=torch.uint8)
+    h2, dz2 = torch.empty(m, n2, device="cuda"), torch.empty(m, n2, device="cuda")
+    pr, dz3 = torch.empty(m, 16, device="cuda"), torch.empty(m, 16, device="cuda")
+    dz1, met = torch.empty(m, n1, device="cuda"), torch.zeros(4, device="cuda")
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    N.check(lib.b200cnn_mlp_head(p(h1), p(w2), p(b2), p(w3), p(b3), p(lab), p(h2), p(pr), p(dz3), p(dz2), p(dz1), p(met), m, n1, n2, nc, 16, st), "mlp_head")
+    rh2 = torch.tanh(h1 @ w2.T + b2)
+    rp = torch.softmax(rh2 @ w3.T + b3, 1)
+    rdz3 = rp - F.one_hot(lab.long(), nc)
+    rdz2 = (rdz3 @ w3) * (1 - rh2 ** 2)
+    rdz1 = (rdz2 @ w2) * (1 - h1 ** 2)
+    for got, want in ((h2, rh2), (pr[:, :nc], rp), (dz3[:, :nc], rdz3), (dz2, rdz2), (dz1, rdz1)):
+        _close(got, want, 5e-3)
+    assert float(pr[:, nc:].abs().max()) == 0.0 if nc < 16 else True
+    got = met.cpu().numpy()
+    assert got[3] == m and got[2] == float((rp.argmax(1) == lab.long()).sum())
+    assert got[0] == pytest.approx(float(-torch.log(rp[torch.arange(m), lab.long()]).sum()), rel=2e-3)

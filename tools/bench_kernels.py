@@ -34,6 +34,10 @@ for backend, bname in ((N.BACKEND_SIMT, "simt"), (N.BACKEND_AUTO, "tc")):
     x, w, b, lab, pr, dz, met = R(B, 200), R(10, 200), R(10), torch.randint(0, 10, (B,), device="cuda", dtype=torch.uint8), R(B, 16), R(B, 16), torch.zeros(4, device="cuda")
     out[f"{bname}.out.softmax"] = timeit(f"{bname} out fwd+softmax+xent", lambda: lib.b200cnn_linear_softmax_xent(p(x), p(w), p(b), p(lab), p(pr), p(dz), p(met), B, 10, 200, 16, st))
 lib.b200cnn_set_backend(N.BACKEND_AUTO)
+h1, w2, b2, w3, b3 = torch.tanh(R(B, 200)), R(200, 200) / 14, R(200), R(10, 200) / 14, R(10)
+lab = torch.randint(0, 10, (B,), device="cuda", dtype=torch.uint8)
+h2, pr, dz3, dz2, dzh1, met = R(B, 200), R(B, 16), R(B, 16), R(B, 200), R(B, 200), torch.zeros(4, device="cuda")
+out["tc.head"] = timeit("tc fused head (fc2+out+softmax+2 dX)", lambda: lib.b200cnn_mlp_head(p(h1), p(w2), p(b2), p(w3), p(b3), p(lab), p(h2), p(pr), p(dz3), p(dz2), p(dzh1), p(met), B, 200, 200, 10, 16, st))
 s1 = N.ConvShape(B, 1, 28, 28, 16, 14, 14, 3, 1, 2); s2 = N.ConvShape(B, 16, 14, 14, 32, 7, 7, 3, 1, 2)
 x8 = torch.randint(0, 256, (B, 784), device="cuda", dtype=torch.uint8)
 w1, b1, a1, dz1 = R(16, 1, 3, 3), R(16), R(B, 14, 14, 16), R(B, 14, 14, 16)
