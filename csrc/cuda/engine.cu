@@ -62,7 +62,7 @@ struct b200cnn_engine {
         cudaGraphExec_t exec[2] = {nullptr, nullptr};
         const void* images = nullptr;
         const uint8_t* labels = nullptr;
-        int batch = 0, is_u8 = 0, backend = -1;
+        int batch = 0, is_u8 = 0, backend = -1, update = 1;
         cudaStream_t stream = nullptr;
         unsigned long last_use = 0;
     };
@@ -524,7 +524,7 @@ extern "C" int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream st
 }
 
 static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
-                        cudaStream_t st, int* launches) {
+                        cudaStream_t st, int* launches, bool update = true) {
     const bool head = use_head(e, batch);
     if (!head) {
         if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches)) return rc;
@@ -540,16 +540,33 @@ static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const 
         if (launches) (*launches)++;
     }
     if (int rc = enqueue_backward(e, images, is_u8, batch, st, launches, head)) return rc;
-    return enqueue_update(e, st, launches);
+    return update ? enqueue_update(e, st, launches) : 0;
 }
+
+static int train_step_impl(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch, float lr,
+                           int use_graph, b200cnn_stream stream, bool update);
 
 extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels,
                                          int batch, float lr, int use_graph, b200cnn_stream stream) {
+    return train_step_impl(e, images, x_is_u8, labels, batch, lr, use_graph, stream, true);
+}
+
+// forward + backward only (gradients left in the gradient buffer), graph-captured like a full step: the
+// building block of update paths that live outside the engine (the NCCL baseline).
+extern "C" int b200cnn_engine_forward_backward(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels,
+                                               int batch, int use_graph, b200cnn_stream stream) {
+    if (e->comm) return set_error(kInvalidValue, "engine_forward_backward: detach the fused communicator first");
+    return train_step_impl(e, images, x_is_u8, labels, batch, 0.0f, use_graph, stream, false);
+}
+
+static int train_step_impl(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch, float lr,
+                           int use_graph, b200cnn_stream stream, bool update) {
     if (batch < 1 || batch > e->max_batch) return set_error(kInvalidValue, "engine_train_step: batch %d outside [1, %d]", batch, e->max_batch);
     if (!labels) return set_error(kInvalidValue, "engine_train_step: labels are required");
     if (int rc = ensure_buffers(e)) return rc;
     cudaStream_t st = as_stream(stream);
-    if (int rc = set_lr(e, lr, st)) return rc;
+    if (update)
+        if (int rc = set_lr(e, lr, st)) return rc;
     e->last_images = images;
     e->last_is_u8 = x_is_u8;
     e->last_batch = batch;
@@ -559,7 +576,7 @@ extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, 
     const int par = e->comm ? comm_parity(e->comm) : 0;
     if (!use_graph) {
         int launches = 0;
-        const int rc = enqueue_step(e, images, x_is_u8, labels, batch, st, &launches);
+        const int rc = enqueue_step(e, images, x_is_u8, labels, batch, st, &launches, update);
         e->launches_per_step = launches;
         return rc;
     }
@@ -567,7 +584,7 @@ extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, 
     b200cnn_engine::GraphEntry* ge = nullptr;
     for (auto& c : e->graphs)
         if (c.images == images && c.labels == labels && c.batch == batch && c.is_u8 == x_is_u8 && c.stream == st &&
-            c.backend == current_backend() && (c.exec[0] || c.exec[1]))
+            c.backend == current_backend() && c.update == int(update) && (c.exec[0] || c.exec[1]))
             ge = &c;
     if (!ge) {
         ge = &e->graphs[0];
@@ -584,6 +601,7 @@ extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, 
         ge->is_u8 = x_is_u8;
         ge->stream = st;
         ge->backend = current_backend();
+        ge->update = int(update);
     }
     ge->last_use = ++e->graph_clock;
     if (!ge->exec[par]) {
@@ -591,7 +609,7 @@ extern "C" int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, 
         cudaGraph_t graph = nullptr;
         B200CNN_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
         int launches = 0;
-        const int rc = enqueue_step(e, images, x_is_u8, labels, batch, st, &launches);
+        const int rc = enqueue_step(e, images, x_is_u8, labels, batch, st, &launches, update);
         const cudaError_t ce = cudaStreamEndCapture(st, &graph);
         if (rc) {
             if (graph) cudaGraphDestroy(graph);

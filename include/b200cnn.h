@@ -199,6 +199,10 @@ int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream stream);
  * replayed as a CUDA graph. */
 int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch,
                               float lr, int use_graph, b200cnn_stream stream);
+/* forward + backward only, graph-captured like a full step; gradients stay in the gradient buffer (for update
+ * paths outside the engine, e.g. the NCCL all-reduce baseline). */
+int b200cnn_engine_forward_backward(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch,
+                                    int use_graph, b200cnn_stream stream);
 /* metrics: {sum CE, sum MSE, #correct, #samples} accumulated since the last reset (device buffer). */
 float* b200cnn_engine_metrics(b200cnn_engine* e);
 int b200cnn_engine_reset_metrics(b200cnn_engine* e, b200cnn_stream stream);

@@ -150,6 +150,13 @@ class Engine:
                 _stream_ptr(stream)),
             "train_step")
 
+    def forward_backward(self, images, labels, use_graph=True, stream=None):
+        """forward + backward as one (graph-captured) launch; gradients are left in the gradient buffer."""
+        ptr, is_u8, batch = self._img_ptr(images)
+        assert labels.dtype == torch.uint8 and labels.is_cuda and labels.numel() == batch
+        N.check(self.lib.b200cnn_engine_forward_backward(self.handle, ptr, is_u8, C.c_void_p(labels.data_ptr()), batch,
+                                                         1 if use_graph else 0, _stream_ptr(stream)), "forward_backward")
+
     @property
     def launches_per_step(self):
         return self.lib.b200cnn_engine_launches_per_step(self.handle)

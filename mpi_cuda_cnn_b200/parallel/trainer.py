@@ -55,8 +55,8 @@ class DataParallelTrainer:
             # 1/world is applied inside the fused kernel.
             self.engine.train_step(images, labels, lr, use_graph=use_graph)
         else:
-            self.engine.forward(images, labels)
-            self.engine.backward()
+            # the baseline gets the same graph-captured forward + backward as the product; only the update differs
+            self.engine.forward_backward(images, labels, use_graph=use_graph)
             g = self.flat_grads()
             if self.world > 1:
                 dist.all_reduce(g)
