@@ -255,8 +255,14 @@ int resolve_algo(const b200cnn_comm* c, int algo, size_t count, int op) {
     if (algo == B200CNN_ALGO_AUTO) algo = c->algo;
     if (c->view.world == 1) return B200CNN_ALGO_ONE_SHOT;
     if (algo == B200CNN_ALGO_AUTO) {
-        if (count * sizeof(float) <= 256 * 1024) algo = B200CNN_ALGO_ONE_SHOT;
-        else algo = c->view.mc_region ? B200CNN_ALGO_NVLS : B200CNN_ALGO_TWO_SHOT;
+        // Measured crossovers on 8xB200 (profiles/allreduce_sweep_w*.json and in-step runs): one-shot wins while
+        // (W-1) x bytes of peer loads cost less than a second flag exchange; NVLS wins once the message is large
+        // enough for the switch reduction to matter; two-shot in between.
+        const size_t bytes = count * sizeof(float);
+        const size_t one_shot_max = c->view.world <= 2 ? (4u << 20) : c->view.world <= 4 ? (256u << 10) : (8u << 10);
+        if (bytes <= one_shot_max) algo = B200CNN_ALGO_ONE_SHOT;
+        else if (bytes >= (8u << 20) && c->view.mc_region) algo = B200CNN_ALGO_NVLS;
+        else algo = B200CNN_ALGO_TWO_SHOT;
     }
     if (algo == B200CNN_ALGO_NVLS && !c->view.mc_region) algo = B200CNN_ALGO_TWO_SHOT;
     // The in-place one-shot all-reduce keeps at most 4 float4 per thread in registers.

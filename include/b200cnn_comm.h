@@ -58,8 +58,8 @@ int b200cnn_comm_world(const b200cnn_comm* c);
 int b200cnn_comm_has_multicast(const b200cnn_comm* c);
 float* b200cnn_comm_params(b200cnn_comm* c);
 float* b200cnn_comm_grads(b200cnn_comm* c, int parity);
-/* Algorithm used by the engine's per-layer launches (AUTO: one-shot up to 256 KiB, then NVLS if
- * available, else two-shot). */
+/* Algorithm used by the engine's bucket launches.  AUTO picks by measured crossover: one-shot up to 4 MiB / 256 KiB /
+ * 8 KiB at world 2 / 4 / 8, NVLS from 8 MiB when a multicast mapping exists, two-shot in between. */
 int b200cnn_comm_set_algo(b200cnn_comm* c, int algo);
 /* 0 if no kernel of this communicator ever timed out waiting for a peer; the kernels give up after
  * ~2 s instead of hanging the GPU. */
