@@ -141,11 +141,30 @@ def run_b200(args):
         ys = torch.empty((BATCH,), dtype=torch.uint8, device=device)
         engine.reset_metrics()
 
-        def device_step(i):
-            F200.gather_batch(data_x, data_y, BATCH, seed=3, step=i, out=(xs, ys))
-            step(xs, ys)
+        # Data loading overlapped with training: batch i+1 is gathered on a second stream into the other staging
+        # buffer while step i runs (the engine keeps one captured graph per staging buffer).
+        xs2, ys2 = torch.empty_like(xs), torch.empty_like(ys)
+        dstage = [(xs, ys), (xs2, ys2)]
+        gather_stream = torch.cuda.Stream(device=device)
+        gathered = [torch.cuda.Event(), torch.cuda.Event()]
+        freed = [torch.cuda.Event(), torch.cuda.Event()]
+        for ev in freed:
+            ev.record(stream)
 
+        def device_gather(i):
+            with torch.cuda.stream(gather_stream):
+                gather_stream.wait_event(freed[i % 2])
+                F200.gather_batch(data_x, data_y, BATCH, seed=3, step=i, out=dstage[i % 2])
+                gathered[i % 2].record(gather_stream)
+
+        def device_step(i):
+            stream.wait_event(gathered[i % 2])
+            step(*dstage[i % 2])
+            freed[i % 2].record(stream)
+
+        device_gather(0)
         for i in range(W):
+            device_gather(i + 1)
             device_step(i)
         stream.synchronize()
         barrier()
@@ -154,10 +173,13 @@ def run_b200(args):
         with ClockSampler(gpu_index=device.index or 0) as clocks:
             ev0.record(stream)
             for i in range(K):
+                if i + 1 < K:
+                    device_gather(W + i + 1)
                 device_step(W + i)
             ev1.record(stream)
             stream.synchronize()
         barrier()
+        gather_stream.synchronize()
         ms = ev0.elapsed_time(ev1)
         m_dev = engine.read_metrics()
 

@@ -47,7 +47,8 @@ struct b200cnn_engine {
     float* grads = nullptr;
     bool own_buffers = false;
     void* arena = nullptr;       // activations, dz, scratch, metrics, hyper-parameters
-    float* scratch = nullptr;
+    float* scratch = nullptr;   // partial sums of the conv weight-gradient kernels (layers >= 2)
+    float* scratch1 = nullptr;  // same for layer 1, which may run concurrently with layer 2's
     size_t scratch_bytes = 0;
     float* metrics = nullptr;    // [4]
     float* lr_dev = nullptr;     // [1], read by the graph-captured update
@@ -228,20 +229,27 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
         if (l.d.type != B200CNN_LAYER_FULL && l.d.type != B200CNN_LAYER_CONV)
             return set_error(kInvalidValue, "engine: bad layer type %d", l.d.type);
 
-        // l.dz is complete on `st` here: fork the weight-gradient work.
-        B200CNN_CUDA(cudaEventRecord(e->ev_dz, st));
-        B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_dz, 0));
+        // l.dz is complete on `st` here: fork the weight-gradient work.  The first parameterised layer has no
+        // data gradient to compute, so its weight gradient IS the tail of the critical path: it stays on `st`
+        // instead of queueing behind the other weight-gradient kernels on the side stream.
+        const bool tail = (li == 1);
+        cudaStream_t ws = tail ? st : side;
+        if (!tail) {
+            B200CNN_CUDA(cudaEventRecord(e->ev_dz, st));
+            B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_dz, 0));
+        }
         if (l.d.type == B200CNN_LAYER_FULL) {
             rc = b200cnn_linear_bwd_weight(l.dz, static_cast<const float*>(in), grads + l.w_off, grads + l.b_off, 0, batch,
-                                           l.nnodes, p.nnodes, l.ld, side);
+                                           l.nnodes, p.nnodes, l.ld, ws);
             if (launches) (*launches)++;
         } else {
             const b200cnn_conv_shape s = conv_shape(p, l, batch);
             if (fast && li <= 2)
-                rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/li == 2, grads + l.w_off, grads + l.b_off, 0, e->scratch,
-                                          reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, side);
+                rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/li == 2, grads + l.w_off, grads + l.b_off, 0,
+                                          li == 1 ? e->scratch1 : e->scratch, reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, ws);
             else
-                rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0, e->scratch, &s, side);
+                rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0,
+                                              li == 1 ? e->scratch1 : e->scratch, &s, ws);
             if (launches) (*launches) += 2;
         }
         if (rc) return rc;
@@ -262,7 +270,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             if (launches) (*launches)++;
         }
         if (e->comm) {
-            if (li > 1) {
+            if (li > 1 || tail) {  // the update hook (on the side stream) follows everything issued on `st` for this layer
                 B200CNN_CUDA(cudaEventRecord(e->ev_data, st));
                 B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_data, 0));
             }
@@ -376,7 +384,7 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
         }
     }
     e->scratch_bytes = round_up(scratch_bytes, 512);
-    const size_t arena_bytes = arena_floats * sizeof(float) + e->scratch_bytes + 1024;  // tail: metrics, lr, counters
+    const size_t arena_bytes = arena_floats * sizeof(float) + 2 * e->scratch_bytes + 1024;  // tail: metrics, lr, counters
     if (cudaMalloc(&e->arena, arena_bytes) != cudaSuccess || cudaMemset(e->arena, 0, arena_bytes) != cudaSuccess) {
         set_error(int(cudaGetLastError()), "engine_create: cannot allocate %zu bytes of activations", arena_bytes);
         delete e;
@@ -403,6 +411,8 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
         return nullptr;
     }
     e->scratch = cur;
+    cur += e->scratch_bytes / sizeof(float);
+    e->scratch1 = cur;
     cur += e->scratch_bytes / sizeof(float);
     e->metrics = cur;
     e->lr_dev = cur + 8;

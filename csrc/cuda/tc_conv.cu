@@ -122,12 +122,15 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a)
     } else if (warp >= 2) {
         const int q = warp & 3;
         const int r = 32 * q + lane;
+        float bias[OC];  // fetched before the accumulator is ready
+#pragma unroll
+        for (int i = 0; i < OC; i++) bias[i] = __ldg(a.bias + i);
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
         const bool live = r < rows;
         const int g = r / pix, p = r % pix;
         float* out = a.y + size_t(n0 + g) * a.ldy + p;
-#pragma unroll 1
+#pragma unroll
         for (int c0 = 0; c0 < OC; c0 += 16) {
             float v[16];
             __syncwarp();
@@ -135,7 +138,7 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a)
             if (live) {
 #pragma unroll
                 for (int i = 0; i < 16; i++)
-                    out[size_t(c0 + i) * pix] = apply_act(a.act, v[i] + __ldg(a.bias + c0 + i));
+                    out[size_t(c0 + i) * pix] = apply_act(a.act, v[i] + bias[c0 + i]);
             }
         }
         __syncwarp();
@@ -302,11 +305,23 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
     } else if (warp >= 2) {
         const int q = warp & 3;
         const int r = 32 * q + lane;
-        mbar_wait(tmem_full_bar, 0);
-        tcgen05_fence_after();
         const bool live = r < rows;
         const int g = r / pix, p = r % pix, j = p / a.ow, i = p % a.ow;
-#pragma unroll 1
+        // Prefetch the ReLU mask source (the previous layer's activations at this thread's four input pixels) before
+        // waiting for the accumulators: 16 independent loads in flight instead of four exposed round trips.
+        float4 msk[4][C / 4];
+        if (live && a.a_prev) {
+#pragma unroll
+            for (int cls = 0; cls < 4; cls++) {
+                const int y = 2 * j + (cls >> 1), x = 2 * i + (cls & 1);
+                const float4* ap = reinterpret_cast<const float4*>(a.a_prev + ((size_t(n0 + g) * a.h + y) * a.w_in + x) * C);
+#pragma unroll
+                for (int k4 = 0; k4 < C / 4; k4++) msk[cls][k4] = (y < a.h && x < a.w_in) ? __ldg(ap + k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        mbar_wait(tmem_full_bar, 0);
+        tcgen05_fence_after();
+#pragma unroll
         for (int cls = 0; cls < 4; cls++) {
             float v[16];
             __syncwarp();
@@ -315,10 +330,9 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
             if (live && y < a.h && x < a.w_in) {
                 const size_t off = ((size_t(n0 + g) * a.h + y) * a.w_in + x) * C;
                 if (a.a_prev) {
-                    const float4* ap = reinterpret_cast<const float4*>(a.a_prev + off);
 #pragma unroll
                     for (int k4 = 0; k4 < C / 4; k4++) {
-                        const float4 av = __ldg(ap + k4);
+                        const float4 av = msk[cls][k4];
                         v[4 * k4 + 0] *= act_grad_from_output(a.act_prev, av.x);
                         v[4 * k4 + 1] *= act_grad_from_output(a.act_prev, av.y);
                         v[4 * k4 + 2] *= act_grad_from_output(a.act_prev, av.z);

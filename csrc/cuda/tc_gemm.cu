@@ -142,6 +142,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     pdl_wait();               // everything above overlapped the previous kernel's tail
     pdl_launch_dependents();  // let the next kernel begin its own prologue
     float rs = 0.0f;          // bias-gradient partial of an epilogue thread (backward-weight only)
+    int label_pre = -1;       // prefetched label of this thread's row (softmax epilogue only)
+    // epilogue operands prefetched while the mainloop runs: activation values (backward-data) or the bias (forward)
+    float auxr[((EPI == kEpiActGrad || EPI == kEpiBiasAct || EPI == kEpiSoftmax) && BLOCK_N <= 64) ? BLOCK_N : 1];
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -216,6 +219,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if (lane == 0) mbar_arrive(&empty_bar[s]);
             }
         }
+        // backward-data: fetch this thread's slice of the activation values (for act') NOW, while TMA and the tensor
+        // core are busy, instead of exposing an L2 round trip per 16-column chunk after the accumulator is ready.
+        constexpr bool kPrefetchAux = (EPI == kEpiActGrad) && BLOCK_N <= 64;
+        if (kPrefetchAux && ep.aux && m0 + row_in_tile < M) {
+            const float* arow = ep.aux + size_t(m0 + row_in_tile) * ep.ld_aux + n0;
+#pragma unroll
+            for (int i = 0; i < (kPrefetchAux ? BLOCK_N : 1); i++) auxr[i] = (n0 + i < N) ? __ldg(arow + i) : 0.0f;
+        }
+        constexpr bool kPrefetchBias = (EPI == kEpiBiasAct || EPI == kEpiSoftmax) && BLOCK_N <= 64;
+        if (kPrefetchBias) {
+#pragma unroll
+            for (int i = 0; i < (kPrefetchBias ? BLOCK_N : 1); i++) auxr[i] = (ep.bias && n0 + i < N) ? __ldg(ep.bias + n0 + i) : 0.0f;
+        }
+        if (EPI == kEpiSoftmax && ep.labels && m0 + row_in_tile < M) label_pre = int(ep.labels[m0 + row_in_tile]);
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
         if (BLOCK_N == 16 && splits > 1) {
@@ -248,7 +265,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
                 for (int i = 0; i < 16; i++)
                     if (i < N) {
-                        v[i] += ep.bias ? __ldg(ep.bias + i) : 0.0f;
+                        v[i] += auxr[i];
                         if (mx < v[i]) {
                             mx = v[i];
                             arg = i;
@@ -262,7 +279,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         sum += v[i];
                     }
                 const float inv = 1.0f / sum;
-                const int label = ep.labels ? int(ep.labels[m]) : -1;
+                const int label = label_pre;
                 float* prow = ep.C + size_t(m) * ep.ldc;
                 float* drow = ep.dz ? ep.dz + size_t(m) * ep.ldc : nullptr;
 #pragma unroll
@@ -293,7 +310,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
             }
         } else
-#pragma unroll 1
+#pragma unroll(BLOCK_N <= 64 ? BLOCK_N / 16 : 1)
         for (int c0 = 0; c0 < BLOCK_N; c0 += 16) {
             float v[16];
             __syncwarp();  // tcgen05.ld is warp-collective: reconverge after the guarded stores below
@@ -315,13 +332,21 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if (EPI == kEpiBiasAct) {
 #pragma unroll
                     for (int i = 0; i < 16; i++)
-                        if (i < valid) v[i] = apply_act(ep.act, v[i] + (ep.bias ? __ldg(ep.bias + n_first + i) : 0.0f));
+                        if (i < valid)
+                            v[i] = apply_act(ep.act, v[i] + (BLOCK_N <= 64 ? auxr[(c0 + i) % (sizeof(auxr) / sizeof(float))]
+                                                                           : (ep.bias ? __ldg(ep.bias + n_first + i) : 0.0f)));
                 } else if (EPI == kEpiActGrad) {
                     if (ep.aux) {
-                        const float* arow = ep.aux + size_t(m) * ep.ld_aux + n_first;
+                        if (EPI == kEpiActGrad && BLOCK_N <= 64) {
 #pragma unroll
-                        for (int i = 0; i < 16; i++)
-                            if (i < valid) v[i] *= act_grad_from_output(ep.act, __ldg(arow + i));
+                            for (int i = 0; i < 16; i++)
+                                if (i < valid) v[i] *= act_grad_from_output(ep.act, auxr[(c0 + i) % (sizeof(auxr) / sizeof(float))]);
+                        } else {
+                            const float* arow = ep.aux + size_t(m) * ep.ld_aux + n_first;
+#pragma unroll
+                            for (int i = 0; i < 16; i++)
+                                if (i < valid) v[i] *= act_grad_from_output(ep.act, __ldg(arow + i));
+                        }
                     }
                 } else if (ep.accumulate) {
 #pragma unroll
