@@ -52,7 +52,8 @@ int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const 
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
 int nhwc_bwd_weight_chunks(int n, int* spb_out);
 int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
-                         float* partials, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st);
+                         float* partials, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st,
+                         float* sgd_w = nullptr, float* sgd_b = nullptr, const float* lr_dev = nullptr);
 int simt_conv2d_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* y, const b200cnn_conv_shape* s,
                     int act, int nhwc_out, cudaStream_t st);
 int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks, int nw, int nb, int accumulate,

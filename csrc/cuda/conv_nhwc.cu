@@ -138,7 +138,8 @@ template <typename TIn>
 __global__ void __launch_bounds__(kC1Threads)
 conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restrict__ dz, float* __restrict__ partials,
                                b200cnn_conv_shape s, int spb, float in_scale, float* __restrict__ dw, float* __restrict__ db,
-                               int accumulate, unsigned* __restrict__ counter) {
+                               int accumulate, unsigned* __restrict__ counter, float* __restrict__ sgd_w,
+                               float* __restrict__ sgd_b, const float* __restrict__ lr_dev) {
     extern __shared__ __align__(16) float sm[];
     const int OC = s.oc, kk = s.k * s.k, pix = s.oh * s.ow, oc4n = OC / 4;
     const int in_sz = s.h * s.w, in_pad = (in_sz + 3) & ~3, out_sz = pix * OC;
@@ -241,7 +242,16 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
         float a = red[t];
         for (int sl = 1; sl < parts; sl++) a += red[sl * nout + t];
         float* dst = t < nw ? (dw ? dw + t : nullptr) : (db ? db + (t - nw) : nullptr);
-        if (dst) *dst = accumulate ? *dst + a : a;
+        if (dst) {
+            a = accumulate ? *dst + a : a;
+            *dst = a;
+        }
+        // Optional fused SGD for this layer: being the last kernel of backward, applying the update here takes a
+        // whole kernel off the end of the step's critical path.
+        if (sgd_w) {
+            float* wdst = t < nw ? sgd_w + t : sgd_b + (t - nw);
+            *wdst -= *lr_dev * a;
+        }
     }
 }
 
@@ -268,7 +278,9 @@ int nhwc_bwd_weight_chunks(int n, int* spb_out) {
 // counter: one zero-initialised word used by the single-channel kernel's "last block reduces" step (it resets
 // itself); NULL = the word right after this layer's partials.
 int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
-                         float* partials, unsigned* counter_in, const b200cnn_conv_shape* s, cudaStream_t st) {
+                         float* partials, unsigned* counter_in, const b200cnn_conv_shape* s, cudaStream_t st, float* sgd_w,
+                         float* sgd_b, const float* lr_dev) {
+    if (sgd_w && s->c != 1) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: the fused update exists only in the single-channel kernel");
     if (!nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: unsupported shape");
     int spb = 1;
     const int chunks = nhwc_bwd_weight_chunks(s->n, &spb);
@@ -284,10 +296,10 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         if (smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: samples do not fit shared memory");
         if (x_is_u8) {
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, dim3(chunks), dim3(kC1Threads), smem, st, static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f, dw, db, accumulate, counter));
+            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<uint8_t>, dim3(chunks), dim3(kC1Threads), smem, st, static_cast<const uint8_t*>(x), dz, partials, *s, spb, 1.0f / 255.0f, dw, db, accumulate, counter, sgd_w, sgd_b, lr_dev));
         } else {
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(kC1Threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f, dw, db, accumulate, counter));
+            B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(kC1Threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f, dw, db, accumulate, counter, sgd_w, sgd_b, lr_dev));
         }
     } else {
         const int work = (s->oc / 4) * (s->c / 4) * kk;

@@ -204,8 +204,10 @@ int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, bool last, cudaSt
 //     wait(dz ready) -> dW/db kernel(s) -> wait(this layer's data gradient issued) -> fused update hook
 // The hook must come after the data-gradient kernel because a two-shot / NVLS update may overwrite the
 // layer's weights on this GPU from a peer.
+int enqueue_sgd_range(b200cnn_engine* e, size_t begin, size_t end, cudaStream_t st, int* launches);
+
 int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch, cudaStream_t st, int* launches,
-                     bool head_done = false) {
+                     bool head_done = false, bool fuse_update = false) {
     auto& L = e->layers;
     float* grads = cur_grads(e);
     const bool fast = use_fast_chain(e);
@@ -244,9 +246,12 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             if (launches) (*launches)++;
         } else {
             const b200cnn_conv_shape s = conv_shape(p, l, batch);
-            if (fast && li <= 2)
+            if (fast && li <= 2) {
+                const bool fuse = fuse_update && li == 1;  // single GPU: this kernel's last block also applies the update
                 rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/li == 2, grads + l.w_off, grads + l.b_off, 0,
-                                          li == 1 ? e->scratch1 : e->scratch, reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, ws);
+                                          li == 1 ? e->scratch1 : e->scratch, reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, ws,
+                                          fuse ? e->params + l.w_off : nullptr, fuse ? e->params + l.b_off : nullptr, e->lr_dev);
+            }
             else
                 rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0,
                                               li == 1 ? e->scratch1 : e->scratch, &s, ws);
@@ -268,6 +273,13 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             }
             if (rc) return rc;
             if (launches) (*launches)++;
+        }
+        if (fuse_update && li == 2) {
+            // Every layer above the first has its gradient (side stream) and nothing reads its weights any more once
+            // this layer's data-gradient kernel (just issued on `st`) is done: update them now, next to the tail.
+            B200CNN_CUDA(cudaEventRecord(e->ev_data, st));
+            B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_data, 0));
+            if ((rc = enqueue_sgd_range(e, size_t(l.w_off), e->flat_floats, side, launches))) return rc;
         }
         if (e->comm) {
             if (li > 1 || tail) {  // the update hook (on the side stream) follows everything issued on `st` for this layer
@@ -303,14 +315,22 @@ __global__ void sgd_dev_lr_kernel(float* __restrict__ w, const float* __restrict
     }
 }
 
-int enqueue_update(b200cnn_engine* e, cudaStream_t st, int* launches) {
-    if (e->comm) return comm_join(e->comm, st);  // per-layer fused updates already enqueued
-    const size_t n4 = e->flat_floats / 4;
+int enqueue_sgd_range(b200cnn_engine* e, size_t begin, size_t end, cudaStream_t st, int* launches) {
+    const size_t n4 = (end - begin) / 4;
     const int blocks = int(std::min<size_t>((n4 + 255) / 256, 148 * 4));
-    B200CNN_CUDA(launch_kernel(sgd_dev_lr_kernel, dim3(blocks), dim3(256), 0, st, e->params, static_cast<const float*>(cur_grads(e)), n4,
-                               static_cast<const float*>(e->lr_dev)));
+    B200CNN_CUDA(launch_kernel(sgd_dev_lr_kernel, dim3(blocks), dim3(256), 0, st, e->params + begin,
+                               static_cast<const float*>(cur_grads(e) + begin), n4, static_cast<const float*>(e->lr_dev)));
     if (launches) (*launches)++;
     return 0;
+}
+
+// True when backward can apply the update itself (single GPU, tensor-core conv chain): layers >= 2 on the side
+// stream as soon as their weights are no longer read, layer 1 inside its weight-gradient kernel.
+bool can_fuse_update(const b200cnn_engine* e) { return !e->comm && use_fast_chain(e) && e->layers[2].nw > 0; }
+
+int enqueue_update(b200cnn_engine* e, cudaStream_t st, int* launches) {
+    if (e->comm) return comm_join(e->comm, st);  // per-layer fused updates already enqueued
+    return enqueue_sgd_range(e, 0, e->flat_floats, st, launches);
 }
 
 int set_lr(b200cnn_engine* e, float lr, cudaStream_t st) {
@@ -549,8 +569,9 @@ static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const 
             return rc;
         if (launches) (*launches)++;
     }
-    if (int rc = enqueue_backward(e, images, is_u8, batch, st, launches, head)) return rc;
-    return update ? enqueue_update(e, st, launches) : 0;
+    const bool fuse = update && can_fuse_update(e);
+    if (int rc = enqueue_backward(e, images, is_u8, batch, st, launches, head, fuse)) return rc;
+    return (update && !fuse) ? enqueue_update(e, st, launches) : 0;
 }
 
 static int train_step_impl(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch, float lr,
