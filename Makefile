@@ -78,6 +78,7 @@ sass: $(LIBDIR)/libb200cnn_cuda.so
 	python tools/sass_summary.py $(OBJDIR)/libb200cnn_cuda.sass profiles/sass > profiles/sass/SUMMARY.md
 
 DATADIR ?= build/data
+NP ?= 8
 get_mnist: $(BINDIR)/mkidx
 	@mkdir -p $(DATADIR)
 	$(BINDIR)/mkidx $(DATADIR) 2000 400
@@ -89,7 +90,7 @@ test_serial: $(BINDIR)/cnn get_mnist
 	$(BINDIR)/cnn --nepoch 1 --timing $(MNIST_ARGS)
 
 test_mpi: $(BINDIR)/cnnmpi get_mnist
-	$(BINDIR)/cnnmpi -np 2 --nepoch 1 --timing $(MNIST_ARGS)
+	$(BINDIR)/cnnmpi -np $(NP) --nepoch 1 --timing $(MNIST_ARGS)
 
 test_cuda: $(BINDIR)/cudacnn get_mnist
 	$(BINDIR)/cudacnn --nepoch 1 --batch-size 256 --timing $(MNIST_ARGS)

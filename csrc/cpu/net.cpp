@@ -1,11 +1,20 @@
 #include "net.hpp"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <limits>
 
 namespace b200cnn {
+
+// Hot loops are compiled twice (baseline x86-64 and AVX2) and dispatched at load time, so one binary runs on the
+// build machine and on the GPU box.  -ffp-contract=off keeps both clones bit-identical (no FMA contraction).
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+#define B200CNN_HOT __attribute__((target_clones("avx2", "default")))
+#else
+#define B200CNN_HOT
+#endif
 
 Layer& Net::push(LayerType t, int d, int w, int h, size_t nb, size_t nw) {
     layers_.emplace_back();
@@ -76,18 +85,38 @@ Net Net::mnist(GlibcRand& rng, Quirks q) {
 // layer of the net uses softmax whose "gradient" is 1 because learn_outputs feeds it
 // (softmax - onehot), the exact cross-entropy gradient w.r.t. the logits.
 // ---------------------------------------------------------------------------------------------
-void Net::forward_full(size_t li) {
+B200CNN_HOT void Net::forward_full(size_t li) {
     Layer& self = layers_[li];
     const Layer& prev = layers_[li - 1];
     const int nout = self.nnodes(), nin = prev.nnodes();
     const double* x = prev.outputs.data();
     const double* w = self.weights.data();
+    const bool exact_order = quirks_.shared_conv_slice || quirks_.early_update || quirks_.softmax_max_m1;
     for (int i = 0; i < nout; i++, w += nin) {
-        double acc = self.biases[i];
-        // One sequential accumulator: the summation order is part of the contract with the
-        // reference oracle (bit-identical logits in quirks mode).
-        for (int j = 0; j < nin; j++) acc += x[j] * w[j];
-        self.outputs[i] = acc;
+        if (exact_order) {
+            // One sequential accumulator: the summation order is part of the contract with the
+            // reference oracle (bit-identical logits in quirks mode).
+            double acc = self.biases[i];
+            for (int j = 0; j < nin; j++) acc += x[j] * w[j];
+            self.outputs[i] = acc;
+        } else {
+            // Eight independent partial sums: the dot product is add-latency bound otherwise.
+            double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, a6 = 0, a7 = 0;
+            int j = 0;
+            for (; j + 8 <= nin; j += 8) {
+                a0 += x[j] * w[j];
+                a1 += x[j + 1] * w[j + 1];
+                a2 += x[j + 2] * w[j + 2];
+                a3 += x[j + 3] * w[j + 3];
+                a4 += x[j + 4] * w[j + 4];
+                a5 += x[j + 5] * w[j + 5];
+                a6 += x[j + 6] * w[j + 6];
+                a7 += x[j + 7] * w[j + 7];
+            }
+            double acc = self.biases[i] + (((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7)));
+            for (; j < nin; j++) acc += x[j] * w[j];
+            self.outputs[i] = acc;
+        }
     }
     if (li + 1 == layers_.size()) {
         double m = quirks_.softmax_max_m1 ? -1.0 : -std::numeric_limits<double>::infinity();
@@ -112,7 +141,7 @@ void Net::forward_full(size_t li) {
     }
 }
 
-void Net::backward_full(size_t li) {
+B200CNN_HOT void Net::backward_full(size_t li) {
     Layer& self = layers_[li];
     Layer& prev = layers_[li - 1];
     const int nout = self.nnodes(), nin = prev.nnodes();
@@ -134,7 +163,100 @@ void Net::backward_full(size_t li) {
 // ---------------------------------------------------------------------------------------------
 // Convolution + ReLU, CHW single image, weights [out_c][in_c][ky][kx], zero padding.
 // ---------------------------------------------------------------------------------------------
+namespace {
+// Valid output range [lo, hi) along one axis for filter offset d: 0 <= o*stride - pad + d < in.
+inline void tap_range(int d, int stride, int pad, int in, int out, int& lo, int& hi) {
+    lo = std::max(0, (pad - d + stride - 1) / stride);
+    hi = std::min(out, (in - 1 + pad - d) / stride + 1);
+}
+}  // namespace
+
+// Clean-mode convolution: one (out-channel, in-channel, tap) at a time over the whole output plane.  No bounds
+// checks inside the pixel loops (the valid range per tap is computed once), so the compiler keeps them tight.
+B200CNN_HOT void Net::forward_conv_fast(size_t li) {
+    Layer& self = layers_[li];
+    const Layer& prev = layers_[li - 1];
+    const int k = self.kernsize, kk = k * k, s = self.stride, pad = self.padding;
+    const int ow = self.width, oh = self.height, iw = prev.width, ih = prev.height;
+    for (int z1 = 0; z1 < self.depth; z1++) {
+        double* out = &self.outputs[size_t(z1) * ow * oh];
+        std::fill(out, out + ow * oh, self.biases[z1]);
+        for (int z0 = 0; z0 < prev.depth; z0++) {
+            const double* in = &prev.outputs[size_t(z0) * iw * ih];
+            const double* w = &self.weights[(size_t(z1) * prev.depth + z0) * kk];
+            for (int dy = 0; dy < k; dy++) {
+                int y_lo, y_hi;
+                tap_range(dy, s, pad, ih, oh, y_lo, y_hi);
+                for (int dx = 0; dx < k; dx++) {
+                    int x_lo, x_hi;
+                    tap_range(dx, s, pad, iw, ow, x_lo, x_hi);
+                    const double wv = w[dy * k + dx];
+                    for (int y1 = y_lo; y1 < y_hi; y1++) {
+                        const double* irow = in + (y1 * s - pad + dy) * iw - pad + dx;
+                        double* orow = out + y1 * ow;
+                        for (int x1 = x_lo; x1 < x_hi; x1++) orow[x1] += irow[x1 * s] * wv;
+                    }
+                }
+            }
+        }
+        double* g = &self.gradients[size_t(z1) * ow * oh];
+        for (int i = 0; i < ow * oh; i++) {
+            const double v = (0 < out[i]) ? out[i] : 0;
+            out[i] = v;
+            g[i] = (0 < v) ? 1 : 0;
+        }
+    }
+}
+
+B200CNN_HOT void Net::backward_conv_fast(size_t li) {
+    Layer& self = layers_[li];
+    Layer& prev = layers_[li - 1];
+    std::fill(prev.errors.begin(), prev.errors.end(), 0.0);
+    const int k = self.kernsize, kk = k * k, s = self.stride, pad = self.padding;
+    const int ow = self.width, oh = self.height, iw = prev.width, ih = prev.height;
+    std::vector<double>& dnet = scratch_;
+    dnet.resize(size_t(ow) * oh);
+    for (int z1 = 0; z1 < self.depth; z1++) {
+        const double* err = &self.errors[size_t(z1) * ow * oh];
+        const double* grad = &self.gradients[size_t(z1) * ow * oh];
+        double bsum = 0;
+        for (int i = 0; i < ow * oh; i++) {
+            dnet[i] = err[i] * grad[i];
+            bsum += dnet[i];
+        }
+        self.u_biases[z1] += bsum;
+        for (int z0 = 0; z0 < prev.depth; z0++) {
+            const double* in = &prev.outputs[size_t(z0) * iw * ih];
+            double* perr = &prev.errors[size_t(z0) * iw * ih];
+            const double* w = &self.weights[(size_t(z1) * prev.depth + z0) * kk];
+            double* uw = &self.u_weights[(size_t(z1) * prev.depth + z0) * kk];
+            for (int dy = 0; dy < k; dy++) {
+                int y_lo, y_hi;
+                tap_range(dy, s, pad, ih, oh, y_lo, y_hi);
+                for (int dx = 0; dx < k; dx++) {
+                    int x_lo, x_hi;
+                    tap_range(dx, s, pad, iw, ow, x_lo, x_hi);
+                    const double wv = w[dy * k + dx];
+                    double acc = 0;
+                    for (int y1 = y_lo; y1 < y_hi; y1++) {
+                        const int off = (y1 * s - pad + dy) * iw - pad + dx;
+                        const double* irow = in + off;
+                        double* erow = perr + off;
+                        const double* drow = dnet.data() + y1 * ow;
+                        for (int x1 = x_lo; x1 < x_hi; x1++) {
+                            erow[x1 * s] += wv * drow[x1];
+                            acc += drow[x1] * irow[x1 * s];
+                        }
+                    }
+                    uw[dy * k + dx] += acc;
+                }
+            }
+        }
+    }
+}
+
 void Net::forward_conv(size_t li) {
+    if (!quirks_.shared_conv_slice) return forward_conv_fast(li);
     Layer& self = layers_[li];
     const Layer& prev = layers_[li - 1];
     const int k = self.kernsize, kk = k * k;
@@ -170,6 +292,7 @@ void Net::forward_conv(size_t li) {
 }
 
 void Net::backward_conv(size_t li) {
+    if (!quirks_.shared_conv_slice) return backward_conv_fast(li);
     Layer& self = layers_[li];
     Layer& prev = layers_[li - 1];
     for (double& e : prev.errors) e = 0;

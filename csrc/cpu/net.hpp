@@ -90,12 +90,15 @@ private:
     void backward_full(size_t li);
     void forward_conv(size_t li);
     void backward_conv(size_t li);
+    void forward_conv_fast(size_t li);   // clean mode: tap-outermost, branch-free pixel loops
+    void backward_conv_fast(size_t li);
     void forward_pool(size_t li);
     void backward_pool(size_t li);
     Layer& push(LayerType t, int d, int w, int h, size_t nb, size_t nw);
 
     std::vector<Layer> layers_;
     Quirks quirks_;
+    std::vector<double> scratch_;  // dLoss/d(pre-activation) of one output plane (backward_conv_fast)
 };
 
 }  // namespace b200cnn
