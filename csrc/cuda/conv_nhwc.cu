@@ -282,6 +282,11 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
                          float* sgd_b, const float* lr_dev) {
     if (sgd_w && s->c != 1) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: the fused update exists only in the single-channel kernel");
     if (!nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: unsupported shape");
+    // Scratch layout: [128-byte header | partial sums].  The header's first word is the completion counter of the
+    // single-channel kernel; it resets itself, and no kernel writes partial sums over it, so one scratch buffer can
+    // be shared by the layers of a network as long as it was zeroed once.
+    unsigned* header = reinterpret_cast<unsigned*>(partials);
+    partials += 32;
     int spb = 1;
     const int chunks = nhwc_bwd_weight_chunks(s->n, &spb);
     const int kk = s->k * s->k, nw = s->oc * s->c * kk;
@@ -291,7 +296,7 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         const int items = (s->oc / 4) * (kk + 1);
         if (items > kC1Threads || nout > kC1Threads) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: layer too large for the single-channel kernel");
         const int slices = kC1Threads / items;
-        unsigned* counter = counter_in ? counter_in : reinterpret_cast<unsigned*>(partials + size_t(chunks) * nout);
+        unsigned* counter = counter_in ? counter_in : header;
         const size_t smem = (size_t(spb) * (((s->h * s->w + 3) & ~3) + size_t(s->oh) * s->ow * s->oc) + size_t(std::max(slices, kC1Threads / nout)) * nout) * sizeof(float);
         if (smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: samples do not fit shared memory");
         if (x_is_u8) {

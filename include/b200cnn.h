@@ -86,7 +86,8 @@ int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz, int dz_is_chw, const float*
                                     float* dx_nhwc, const b200cnn_conv_shape* s, b200cnn_stream stream);
 /* dw (OIHW) / db for NHWC activations: x NHWC (or a 1-channel image, uint8 allowed), dz NHWC or CHW.
  * Register-tiled CUDA-core kernel + fixed-order reduction of per-block partial sums held in `scratch`
- * (zero the scratch once after allocating it: its last word is a self-resetting completion counter). */
+ * (zero the scratch once after allocating it: its first 128 bytes hold a self-resetting completion counter; the
+ * buffer may then be shared by several layers as long as their calls do not overlap on the GPU). */
 size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s);
 int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const float* dz, int dz_is_chw, float* dw, float* db,
                                    int accumulate, void* scratch, const b200cnn_conv_shape* s, b200cnn_stream stream);
