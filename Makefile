@@ -2,7 +2,7 @@
 # flag, no -arch, and no rule for the MPI+GPU program).
 #
 #   make cpu        libb200cnn_cpu.so + bin/cnn bin/cnnmpi bin/mkidx
-#   make cuda       libb200cnn_cuda.so (sm_100a kernels, engine, comm) + bin/cudacnn
+#   make cuda       libb200cnn_cuda.so (sm_100a kernels, engine, comm) + bin/cudacnn + bin/cudampi
 #   make all        both
 #   make sass       SASS / resource listings of every kernel under profiles/sass/
 #   make test_serial / test_mpi / test_cuda    the reference's run targets on synthetic data
@@ -36,7 +36,7 @@ all: cpu cuda
 
 cpu: $(LIBDIR)/libb200cnn_cpu.so $(BINDIR)/cnn $(BINDIR)/cnnmpi $(BINDIR)/mkidx
 
-cuda: $(LIBDIR)/libb200cnn_cuda.so $(BINDIR)/cudacnn
+cuda: $(LIBDIR)/libb200cnn_cuda.so $(BINDIR)/cudacnn $(BINDIR)/cudampi
 
 $(OBJDIR)/cpu/%.o: csrc/cpu/%.cpp $(wildcard csrc/cpu/*.hpp) include/b200cnn_cpu.h
 	@mkdir -p $(dir $@)
@@ -70,6 +70,11 @@ $(BINDIR)/cudacnn: csrc/apps/cudacnn_main.cpp $(LIBDIR)/libb200cnn_cuda.so $(OBJ
 	@mkdir -p $(BINDIR)
 	$(CXX) $(CXXFLAGS) -Iinclude -I/usr/local/cuda/include -o $@ csrc/apps/cudacnn_main.cpp $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o \
 	    -L$(LIBDIR) -lb200cnn_cuda -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$$ORIGIN/../$(LIBDIR)'
+
+$(BINDIR)/cudampi: csrc/apps/cudampi_main.cpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o $(OBJDIR)/cpu/comm.o
+	@mkdir -p $(BINDIR)
+	$(CXX) $(CXXFLAGS) -Iinclude -I/usr/local/cuda/include -o $@ csrc/apps/cudampi_main.cpp $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o $(OBJDIR)/cpu/comm.o \
+	    -L$(LIBDIR) -lb200cnn_cuda -L/usr/local/cuda/lib64 -lcudart -lrt -Wl,-rpath,'$$ORIGIN/../$(LIBDIR)'
 
 sass: $(LIBDIR)/libb200cnn_cuda.so
 	@mkdir -p profiles/sass $(OBJDIR)

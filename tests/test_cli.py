@@ -60,3 +60,21 @@ def test_cudampi_two_gpus(dataset_paths, repo_root):
     assert len(sums) == 2 and sums[0] == sums[1]
     assert re.search(r"^0 0 100$", r.stderr, re.M) and re.search(r"^1 100 200$", r.stderr, re.M)
     assert int(re.search(r"ncorrect=(\d+)", r.stderr).group(1)) >= 45
+
+
+@pytest.mark.gpu
+def test_native_cudampi_two_gpus(dataset_paths, repo_root):
+    """The native launcher: fork per GPU, CUDA-IPC regions, fused NVLink update — no Python, MPI or NCCL involved."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    exe = os.path.join(repo_root, "bin", "cudampi")
+    assert _run([exe], repo_root).returncode == 100
+    r = _run([exe, "-np", "2", "--nepoch", "20", "--batch-size", "50", "--rate", "0.3", "--timing"] + dataset_paths, repo_root)
+    assert r.returncode == 0, r.stderr
+    sums = re.findall(r"rank \d param_checksum=(\S+)", r.stderr)
+    assert len(sums) == 2 and sums[0] == sums[1]  # replicas bitwise identical
+    assert re.search(r"^0 0 100$", r.stderr, re.M) and re.search(r"^1 100 200$", r.stderr, re.M)
+    assert int(re.search(r"ncorrect=(\d+)", r.stderr).group(1)) >= 45
+    assert "train_images_per_sec=" in r.stderr
