@@ -205,6 +205,8 @@ def run_b200(args):
             ev.record(stream)
 
         def e2e_upload(i):
+            if mode == "fused":
+                return  # train_step_host copies on the engine's own copy stream
             sx, sy = stage[i % 2]
             with torch.cuda.stream(copy_stream):
                 copy_stream.wait_event(consumed[i % 2])  # the step that last read this buffer has finished
@@ -213,11 +215,16 @@ def run_b200(args):
                 copied[i % 2].record(copy_stream)
 
         def e2e_enqueue(i):
-            sx, sy = stage[i % 2]
-            stream.wait_event(copied[i % 2])
-            step(sx, sy)
-            consumed[i % 2].record(stream)
-            loss_host[i % 2].copy_(metrics, non_blocking=True)
+            if mode == "fused":
+                # the public host-fed step: H2D of this step's inputs (engine's copy stream, double-buffered), the
+                # captured step, D2H of the loss — one native call, nothing blocks
+                engine.train_step_host(host_x[i % pool], host_y[i % pool], RATE / BATCH, metrics_out=loss_host[i % 2], stream=stream)
+            else:
+                sx, sy = stage[i % 2]
+                stream.wait_event(copied[i % 2])
+                step(sx, sy)
+                consumed[i % 2].record(stream)
+                loss_host[i % 2].copy_(metrics, non_blocking=True)
             loss_ready[i % 2].record(stream)
 
         def e2e_collect(i):

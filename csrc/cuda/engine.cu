@@ -77,6 +77,14 @@ struct b200cnn_engine {
     // Data-parallel update buckets: consecutive layers' slices are merged until a bucket holds kBucketFloats,
     // so the number of cross-GPU flag exchanges per step is 2 instead of one per layer.
     long bucket_lo = -1, bucket_hi = -1;
+    // host-fed steps (b200cnn_engine_train_step_host): two device staging slots + a copy stream, so batch i+1 crosses
+    // PCIe while batch i trains
+    uint8_t* stage_x[2] = {nullptr, nullptr};
+    uint8_t* stage_y[2] = {nullptr, nullptr};
+    size_t stage_item = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+    int host_slot = 0;
     bool last_fast = false;   // layout of layer 1's activations in the last forward (NHWC when true)
     bool fast_chain = false;  // conv(C_in=1) -> tc conv3x3 -> FC pattern: NHWC activations + tcgen05 convolutions
 };
@@ -448,6 +456,13 @@ extern "C" void b200cnn_engine_destroy(b200cnn_engine* e) {
         cudaFree(e->params);
         cudaFree(e->grads);
     }
+    for (int i = 0; i < 2; i++) {
+        if (e->stage_x[i]) cudaFree(e->stage_x[i]);
+        if (e->stage_y[i]) cudaFree(e->stage_y[i]);
+        if (e->ev_copied[i]) cudaEventDestroy(e->ev_copied[i]);
+        if (e->ev_consumed[i]) cudaEventDestroy(e->ev_consumed[i]);
+    }
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     if (e->ev_dz) cudaEventDestroy(e->ev_dz);
     if (e->ev_data) cudaEventDestroy(e->ev_data);
     if (e->ev_side) cudaEventDestroy(e->ev_side);
@@ -653,6 +668,48 @@ static int train_step_impl(b200cnn_engine* e, const void* images, int x_is_u8, c
         e->launches_per_step = launches;
     }
     B200CNN_CUDA(cudaGraphLaunch(ge->exec[par], st));
+    return 0;
+}
+
+// One training step fed from (pinned) host memory: the step's inputs are copied to a device staging slot on a
+// copy stream, the captured step runs on `stream`, and the metrics are copied back to `metrics_host`.  Nothing here
+// blocks the host; with two staging slots the copy of batch i+1 overlaps the training of batch i when the caller
+// issues steps back to back.  The caller synchronises (stream or event) before reading `metrics_host`.
+extern "C" int b200cnn_engine_train_step_host(b200cnn_engine* e, const void* images_host, int x_is_u8, const uint8_t* labels_host,
+                                              int batch, float lr, float* metrics_host, b200cnn_stream stream) {
+    if (batch < 1 || batch > e->max_batch) return set_error(kInvalidValue, "engine_train_step_host: batch %d outside [1, %d]", batch, e->max_batch);
+    cudaStream_t st = as_stream(stream);
+    if (st == nullptr) return set_error(kInvalidValue, "engine_train_step_host: needs a non-default stream");
+    const EngineLayer& in = e->layers[0];
+    const size_t item = size_t(in.nnodes) * (x_is_u8 ? 1 : sizeof(float));
+    if (!e->copy_stream) {
+        B200CNN_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) {
+            B200CNN_CUDA(cudaEventCreateWithFlags(&e->ev_copied[i], cudaEventDisableTiming));
+            B200CNN_CUDA(cudaEventCreateWithFlags(&e->ev_consumed[i], cudaEventDisableTiming));
+        }
+    }
+    if (e->stage_item < item) {  // first call (or a wider input type): (re)allocate the staging slots
+        B200CNN_CUDA(cudaDeviceSynchronize());
+        for (int i = 0; i < 2; i++) {
+            if (e->stage_x[i]) cudaFree(e->stage_x[i]);
+            if (e->stage_y[i]) cudaFree(e->stage_y[i]);
+            B200CNN_CUDA(cudaMalloc(&e->stage_x[i], size_t(e->max_batch) * item));
+            B200CNN_CUDA(cudaMalloc(&e->stage_y[i], size_t(e->max_batch)));
+            B200CNN_CUDA(cudaEventRecord(e->ev_consumed[i], st));
+        }
+        e->stage_item = item;
+    }
+    const int slot = e->host_slot;
+    e->host_slot ^= 1;
+    B200CNN_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_consumed[slot], 0));  // the step that last read this slot is done
+    B200CNN_CUDA(cudaMemcpyAsync(e->stage_x[slot], images_host, size_t(batch) * item, cudaMemcpyHostToDevice, e->copy_stream));
+    B200CNN_CUDA(cudaMemcpyAsync(e->stage_y[slot], labels_host, size_t(batch), cudaMemcpyHostToDevice, e->copy_stream));
+    B200CNN_CUDA(cudaEventRecord(e->ev_copied[slot], e->copy_stream));
+    B200CNN_CUDA(cudaStreamWaitEvent(st, e->ev_copied[slot], 0));
+    if (int rc = b200cnn_engine_train_step(e, e->stage_x[slot], x_is_u8, e->stage_y[slot], batch, lr, 1, stream)) return rc;
+    B200CNN_CUDA(cudaEventRecord(e->ev_consumed[slot], st));
+    if (metrics_host) B200CNN_CUDA(cudaMemcpyAsync(metrics_host, e->metrics, 4 * sizeof(float), cudaMemcpyDeviceToHost, st));
     return 0;
 }
 

@@ -200,6 +200,12 @@ int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream stream);
  * replayed as a CUDA graph. */
 int b200cnn_engine_train_step(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch,
                               float lr, int use_graph, b200cnn_stream stream);
+/* A step fed from pinned HOST memory: copies the inputs to one of two device staging slots on an internal copy
+ * stream (so the next batch's copy overlaps this batch's training), replays the captured step on `stream` and copies
+ * the 4 metrics back to `metrics_host` (pinned; may be NULL).  Never blocks the host; synchronise before reading
+ * `metrics_host`.  The first call allocates the staging slots. */
+int b200cnn_engine_train_step_host(b200cnn_engine* e, const void* images_host, int x_is_u8, const uint8_t* labels_host,
+                                   int batch, float lr, float* metrics_host, b200cnn_stream stream);
 /* forward + backward only, graph-captured like a full step; gradients stay in the gradient buffer (for update
  * paths outside the engine, e.g. the NCCL all-reduce baseline). */
 int b200cnn_engine_forward_backward(b200cnn_engine* e, const void* images, int x_is_u8, const uint8_t* labels, int batch,

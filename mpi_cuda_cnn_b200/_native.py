@@ -156,6 +156,7 @@ def cuda():
     _sig(lib, "b200cnn_engine_backward", i, vp, vp)
     _sig(lib, "b200cnn_engine_sgd", i, vp, f, vp)
     _sig(lib, "b200cnn_engine_train_step", i, vp, vp, i, vp, i, f, i, vp)
+    _sig(lib, "b200cnn_engine_train_step_host", i, vp, vp, i, vp, i, f, vp, vp)
     _sig(lib, "b200cnn_engine_forward_backward", i, vp, vp, i, vp, i, i, vp)
     _sig(lib, "b200cnn_engine_metrics", vp, vp)
     _sig(lib, "b200cnn_engine_reset_metrics", i, vp, vp)

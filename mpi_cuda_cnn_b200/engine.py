@@ -150,6 +150,22 @@ class Engine:
                 _stream_ptr(stream)),
             "train_step")
 
+    def train_step_host(self, images, labels, lr, metrics_out=None, stream=None):
+        """One step fed from pinned HOST tensors (uint8 images [B, features], uint8 labels [B]).
+
+        The engine copies them to a device staging slot on its own copy stream (double-buffered, so issuing steps back
+        to back overlaps the next copy with the current step), replays the captured step, and — if ``metrics_out`` (a
+        pinned float32[4] tensor) is given — copies {sum CE, sum MSE, #correct, #samples} back.  Nothing blocks;
+        synchronise the stream (or an event recorded after this call) before reading ``metrics_out``."""
+        assert not images.is_cuda and images.is_pinned() and not labels.is_cuda and labels.is_pinned()
+        assert labels.dtype == torch.uint8 and images.is_contiguous() and labels.is_contiguous()
+        is_u8 = 1 if images.dtype == torch.uint8 else 0
+        batch = images.shape[0]
+        assert images.numel() == batch * self.in_features and labels.numel() == batch
+        mp = C.c_void_p(metrics_out.data_ptr()) if metrics_out is not None else C.c_void_p(0)
+        N.check(self.lib.b200cnn_engine_train_step_host(self.handle, C.c_void_p(images.data_ptr()), is_u8, C.c_void_p(labels.data_ptr()),
+                                                        batch, float(lr), mp, _stream_ptr(stream)), "train_step_host")
+
     def forward_backward(self, images, labels, use_graph=True, stream=None):
         """forward + backward as one (graph-captured) launch; gradients are left in the gradient buffer."""
         ptr, is_u8, batch = self._img_ptr(images)

@@ -131,3 +131,34 @@ def test_batch_limits_and_errors():
     with pytest.raises(RuntimeError, match="batch"):
         eng.train_step(x, y, 0.1, use_graph=False)
     eng.close()
+
+
+def test_host_fed_step_equals_device_step():
+    """train_step_host (pinned inputs, internal double-buffered staging, async loss read-back) == train_step."""
+    from mpi_cuda_cnn_b200 import Engine
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    B = 64
+    a, b = Engine(max_batch=B), Engine(max_batch=B)
+    a.init_params(seed=0)
+    b.init_params(seed=0)
+    x, y = F200.synthetic_batch(B * 6, seed=9)
+    hx = x.cpu().reshape(6, B, 784).pin_memory()
+    hy = y.cpu().reshape(6, B).pin_memory()
+    loss = [torch.zeros(4).pin_memory() for _ in range(6)]
+    stream = torch.cuda.Stream()
+    xs, ys = torch.empty_like(x[:B]), torch.empty_like(y[:B])
+    with torch.cuda.stream(stream):
+        a.reset_metrics()
+        b.reset_metrics()
+        for i in range(6):  # issued back to back: copies overlap the previous step
+            a.train_step_host(hx[i], hy[i], 0.1 / B, metrics_out=loss[i], stream=stream)
+        for i in range(6):
+            xs.copy_(x[i * B:(i + 1) * B]); ys.copy_(y[i * B:(i + 1) * B])
+            b.train_step(xs, ys, 0.1 / B, use_graph=True, stream=stream)
+        stream.synchronize()
+    assert np.array_equal(a.get_params(), b.get_params())
+    counts = [float(l[3]) for l in loss]
+    assert counts == [B * (i + 1) for i in range(6)]  # cumulative sample counter, read back after every step
+    assert float(loss[5][0]) == pytest.approx(b.read_metrics()["ce_sum"], rel=1e-5)
+    a.close(); b.close()
