@@ -173,6 +173,12 @@ def _cudampi_rank(rank, world, argv):
 
     args = _gpu_parser(True).parse_args(argv)
     rank, world, device = init_distributed()
+    if rank == 0:
+        from .parallel import topology
+
+        topo = topology()
+        print(f"topology: {topo['gpus']} GPUs, NVLinks per GPU {topo['nvlinks']}, all peers reachable: "
+              f"{all(all(r) for r in topo['peer'])}", file=sys.stderr)
     trainer = DataParallelTrainer(rank, world, device, layers=pool_layers() if args.pool else mnist_layers(),
                                   batch=args.batch_size, mode=args.update, seed=args.seed, algo=args.algo)
     rc = _train_gpu(args, rank, world, device, trainer)
