@@ -83,12 +83,12 @@ __device__ __forceinline__ uint32_t* flag_ptr(char* region, int block, int phase
 
 // Cross-rank barrier between the blocks with this blockIdx.x on every rank.  All earlier global
 // writes of the CTA are published (CTA barrier, then a cumulative release at system scope).
-__device__ void signal_and_wait(const CommView& v, int rank, int phase, uint32_t seq) {
+__device__ void signal_and_wait(const CommView& v, int rank, int phase, uint32_t seq, int slot) {
     __syncthreads();
     if (threadIdx.x < v.world && int(threadIdx.x) != rank) {
         const int peer = threadIdx.x;
-        st_release_sys(flag_ptr(v.region[peer], blockIdx.x, phase, rank), seq);
-        const uint32_t* mine = flag_ptr(v.region[rank], blockIdx.x, phase, peer);
+        st_release_sys(flag_ptr(v.region[peer], slot, phase, rank), seq);
+        const uint32_t* mine = flag_ptr(v.region[rank], slot, phase, peer);
         const long long t0 = clock64();
         // (Measured: polling with ld.acquire.sys is ~2 us faster per exchange than relaxed polling followed by
         //  fence.acq_rel.sys, whose system-scope fence alone costs more than the whole spin.)
@@ -131,13 +131,16 @@ __device__ __forceinline__ float4 reduce_ranks(const float4* const* g, int world
 template <int W>
 __global__ void __launch_bounds__(kCommThreads)
 allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ lr_dev, float lr_imm, int algo,
-                 int parity, int op, int root) {
+                 int parity, int op, int root, int block_base) {
     const int rank = v.emulate ? int(blockIdx.y) : v.rank;
     const int world = v.world;
-    uint32_t* seq_slot = v.seq + (v.emulate ? rank : 0) * kMaxBlocks + blockIdx.x;
+    // block_base picks the flag words / sequence counters: two kernels of one communicator may run concurrently
+    // (different streams) when their [block_base, block_base + gridDim.x) ranges are disjoint.
+    const int slot = int(blockIdx.x) + block_base;
+    uint32_t* seq_slot = v.seq + (v.emulate ? rank : 0) * kMaxBlocks + slot;
     const uint32_t seq = *seq_slot + 1;
 
-    signal_and_wait(v, rank, 0, seq);  // every rank's inputs for this call are complete
+    signal_and_wait(v, rank, 0, seq, slot);  // every rank's inputs for this call are complete
 
     const float4* g[kMaxRanks];
 #pragma unroll
@@ -175,7 +178,7 @@ allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ l
             float4 keep[4];
             int nkeep = 0;
             for (size_t i = tid; i < n4 && nkeep < 4; i += nthreads) keep[nkeep++] = reduce_ranks<W>(g, world, i);
-            signal_and_wait(v, rank, 1, seq);
+            signal_and_wait(v, rank, 1, seq, slot);
             nkeep = 0;
             for (size_t i = tid; i < n4 && nkeep < 4; i += nthreads) g_local[i] = keep[nkeep++];
         }
@@ -218,7 +221,7 @@ allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ l
         }
         need_exit_barrier = true;  // all shards must have landed everywhere before anyone moves on
     }
-    if (need_exit_barrier) signal_and_wait(v, rank, 1, seq);
+    if (need_exit_barrier) signal_and_wait(v, rank, 1, seq, slot);
     if (threadIdx.x == 0) *seq_slot = seq;
 }
 
@@ -273,9 +276,10 @@ int resolve_algo(const b200cnn_comm* c, int algo, size_t count, int op) {
 }
 
 int launch(const CommView& v, int ranks_y, size_t off4, size_t n4, const float* lr_dev, float lr, int algo, int parity,
-           int op, int root, int blocks, cudaStream_t st) {
+           int op, int root, int blocks, cudaStream_t st, int block_base = 0) {
+    if (block_base + blocks > kMaxBlocks) return set_error(kInvalidValue, "comm: %d blocks from slot %d exceed the %d flag slots", blocks, block_base, kMaxBlocks);
     const dim3 grid(blocks, ranks_y);
-#define B200CNN_LAUNCH_W(W) allreduce_kernel<W><<<grid, kCommThreads, 0, st>>>(v, off4, n4, lr_dev, lr, algo, parity, op, root)
+#define B200CNN_LAUNCH_W(W) allreduce_kernel<W><<<grid, kCommThreads, 0, st>>>(v, off4, n4, lr_dev, lr, algo, parity, op, root, block_base)
     switch (v.world) {
         case 1: B200CNN_LAUNCH_W(1); break;
         case 2: B200CNN_LAUNCH_W(2); break;
@@ -289,7 +293,7 @@ int launch(const CommView& v, int ranks_y, size_t off4, size_t n4, const float* 
 }
 
 int enqueue(b200cnn_comm* c, size_t offset, size_t count, const float* lr_dev, float lr, int algo, int parity, int op,
-            int root, int max_blocks, cudaStream_t st) {
+            int root, int max_blocks, cudaStream_t st, int block_base = 0) {
     if ((offset | count) & 3) return set_error(kInvalidValue, "comm: offset and count must be multiples of 4 floats");
     if (offset + count > c->flat_floats) return set_error(kInvalidValue, "comm: slice [%zu, %zu) outside the %zu-float buffer", offset, offset + count, c->flat_floats);
     if (parity != 0 && parity != 1) return set_error(kInvalidValue, "comm: parity must be 0 or 1");
@@ -301,7 +305,7 @@ int enqueue(b200cnn_comm* c, size_t offset, size_t count, const float* lr_dev, f
         const size_t need = (n4 + size_t(kCommThreads) * 4 - 1) / (size_t(kCommThreads) * 4);
         if (size_t(blocks) < need) blocks = int(need);
     }
-    return launch(c->view, 1, offset / 4, n4, lr_dev, lr, algo, parity, op, root, blocks, st);
+    return launch(c->view, 1, offset / 4, n4, lr_dev, lr, algo, parity, op, root, blocks, st, block_base);
 }
 
 }  // namespace
@@ -392,9 +396,9 @@ extern "C" int b200cnn_comm_barrier(b200cnn_comm* c, b200cnn_stream stream) {
     return launch(c->view, 1, 0, 0, nullptr, 0.0f, B200CNN_ALGO_ONE_SHOT, 0, kOpBarrier, 0, 1, as_stream(stream));
 }
 
-extern "C" int b200cnn_comm_emulate_allreduce_sgd(int world, void* const* region_ptrs, size_t flat_floats, size_t offset,
-                                                  size_t count, float lr, int algo, int parity, int blocks,
-                                                  uint32_t* seq_scratch, b200cnn_stream stream) {
+extern "C" int b200cnn_comm_emulate_allreduce_sgd_slot(int world, void* const* region_ptrs, size_t flat_floats, size_t offset,
+                                                       size_t count, float lr, int algo, int parity, int blocks,
+                                                       int slot_base, uint32_t* seq_scratch, b200cnn_stream stream) {
     if (world < 1 || world > kMaxRanks || (offset | count) & 3 || offset + count > flat_floats)
         return set_error(kInvalidValue, "comm_emulate: bad arguments");
     if (algo != B200CNN_ALGO_ONE_SHOT && algo != B200CNN_ALGO_TWO_SHOT)
@@ -409,7 +413,14 @@ extern "C" int b200cnn_comm_emulate_allreduce_sgd(int world, void* const* region
     v.grads_off[1] = b200cnn_comm_grads_offset(flat_floats, 1);
     v.seq = seq_scratch;                               // [world][kMaxBlocks]
     v.errflag = seq_scratch + size_t(world) * kMaxBlocks;  // + 1 word
-    return launch(v, world, offset / 4, count / 4, nullptr, lr, algo, parity, kOpSgd, 0, blocks, as_stream(stream));
+    return launch(v, world, offset / 4, count / 4, nullptr, lr, algo, parity, kOpSgd, 0, blocks, as_stream(stream), slot_base);
+}
+
+extern "C" int b200cnn_comm_emulate_allreduce_sgd(int world, void* const* region_ptrs, size_t flat_floats, size_t offset,
+                                                  size_t count, float lr, int algo, int parity, int blocks,
+                                                  uint32_t* seq_scratch, b200cnn_stream stream) {
+    return b200cnn_comm_emulate_allreduce_sgd_slot(world, region_ptrs, flat_floats, offset, count, lr, algo, parity, blocks, 0,
+                                                   seq_scratch, stream);
 }
 
 // ---- engine hooks ---------------------------------------------------------------------------
@@ -420,6 +431,13 @@ int comm_allreduce_sgd_slice(b200cnn_comm* c, size_t offset, size_t count, const
     B200CNN_CUDA(cudaStreamWaitEvent(c->stream, c->ev_fork, 0));
     c->forked = true;
     return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, 16, c->stream);
+}
+
+// Same operation enqueued directly on `st` (no stream hop), on the second flag channel so it may overlap a
+// kernel that comm_allreduce_sgd_slice put on the communicator's own stream.  Used for the last bucket of a step,
+// which sits on the critical path.
+int comm_allreduce_sgd_inline(b200cnn_comm* c, size_t offset, size_t count, const float* lr_dev, cudaStream_t st) {
+    return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, 16, st, kMaxBlocks / 2);
 }
 
 int comm_join(b200cnn_comm* c, cudaStream_t st) {

@@ -77,6 +77,7 @@ struct b200cnn_engine {
     // Data-parallel update buckets: consecutive layers' slices are merged until a bucket holds kBucketFloats,
     // so the number of cross-GPU flag exchanges per step is 2 instead of one per layer.
     long bucket_lo = -1, bucket_hi = -1;
+    long tail_lo = -1, tail_hi = -1;  // last bucket of the step: launched on the main stream after the join
     // host-fed steps (b200cnn_engine_train_step_host): two device staging slots + a copy stream, so batch i+1 crosses
     // PCIe while batch i trains
     uint8_t* stage_x[2] = {nullptr, nullptr};
@@ -198,6 +199,12 @@ int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, bool last, cudaSt
         e->bucket_hi = std::max(e->bucket_hi, end);
     }
     if (!last && e->bucket_hi - e->bucket_lo < kBucketFloats) return 0;
+    if (last) {  // deferred: runs on the main stream right after the side stream has been joined
+        e->tail_lo = e->bucket_lo;
+        e->tail_hi = e->bucket_hi;
+        e->bucket_lo = e->bucket_hi = -1;
+        return 0;
+    }
     const int rc = comm_allreduce_sgd_slice(e->comm, size_t(e->bucket_lo), size_t(e->bucket_hi - e->bucket_lo), e->lr_dev, st);
     e->bucket_lo = e->bucket_hi = -1;
     if (rc) return rc;
@@ -221,6 +228,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
     const bool fast = use_fast_chain(e);
     cudaStream_t side = e->side;
     e->bucket_lo = e->bucket_hi = -1;
+    e->tail_lo = e->tail_hi = -1;
     for (size_t li = L.size() - 1; li >= 1; li--) {
         EngineLayer& l = L[li];
         EngineLayer& p = L[li - 1];
@@ -290,18 +298,26 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             if ((rc = enqueue_sgd_range(e, size_t(l.w_off), e->flat_floats, side, launches))) return rc;
         }
         if (e->comm) {
-            if (li > 1 || tail) {  // the update hook (on the side stream) follows everything issued on `st` for this layer
+            bool last = true;  // no parameterised layer below this one?
+            for (size_t lj = 1; lj < li; lj++) last = last && L[lj].nw == 0;
+            if (!last) {  // the update hook (on the side stream) follows everything issued on `st` for this layer
                 B200CNN_CUDA(cudaEventRecord(e->ev_data, st));
                 B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_data, 0));
             }
-            bool last = true;  // no parameterised layer below this one?
-            for (size_t lj = 1; lj < li; lj++) last = last && L[lj].nw == 0;
             if ((rc = layer_grads_ready(e, l, last, side, launches))) return rc;
         }
     }
     // Join: everything on the side stream is ordered before whatever follows on `st`.
     B200CNN_CUDA(cudaEventRecord(e->ev_side, side));
     B200CNN_CUDA(cudaStreamWaitEvent(st, e->ev_side, 0));
+    if (e->comm && e->tail_lo >= 0) {
+        // The step's last bucket is on the critical path: no stream hops, and it does not queue behind the big
+        // bucket that may still be running on the communicator's stream (separate flag channel).
+        const int rc = comm_allreduce_sgd_inline(e->comm, size_t(e->tail_lo), size_t(e->tail_hi - e->tail_lo), e->lr_dev, st);
+        e->tail_lo = e->tail_hi = -1;
+        if (rc) return rc;
+        if (launches) (*launches)++;
+    }
     return 0;
 }
 

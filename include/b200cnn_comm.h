@@ -98,6 +98,11 @@ int b200cnn_ipc_close(void* ptr);
 int b200cnn_comm_emulate_allreduce_sgd(int world, void* const* region_ptrs, size_t flat_floats, size_t offset,
                                        size_t count, float lr, int algo, int parity, int blocks, uint32_t* seq_scratch,
                                        b200cnn_stream stream);
+/* Same, on flag slots [slot_base, slot_base + blocks): the engine runs a step's last bucket on slots 64.. so it can
+ * overlap a bucket still running on slots 0.. from the communicator's own stream. */
+int b200cnn_comm_emulate_allreduce_sgd_slot(int world, void* const* region_ptrs, size_t flat_floats, size_t offset,
+                                            size_t count, float lr, int algo, int parity, int blocks, int slot_base,
+                                            uint32_t* seq_scratch, b200cnn_stream stream);
 
 #ifdef __cplusplus
 }

@@ -181,6 +181,7 @@ def cuda():
     _sig(lib, "b200cnn_comm_broadcast_params", i, vp, i, vp)
     _sig(lib, "b200cnn_comm_barrier", i, vp, vp)
     _sig(lib, "b200cnn_comm_emulate_allreduce_sgd", i, i, C.POINTER(vp), sz, sz, sz, f, i, i, i, vp, vp)
+    _sig(lib, "b200cnn_comm_emulate_allreduce_sgd_slot", i, i, C.POINTER(vp), sz, sz, sz, f, i, i, i, i, vp, vp)
     _sig(lib, "b200cnn_ipc_alloc", vp, sz)
     _sig(lib, "b200cnn_ipc_free", i, vp)
     _sig(lib, "b200cnn_ipc_get_handle", i, vp, C.c_char_p)

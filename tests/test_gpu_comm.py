@@ -44,7 +44,9 @@ def test_emulated_ranks_one_gpu(world, algo):
         for r in range(world):
             views[r][1][par].copy_(grads[r])
         off, cnt = (0, flat) if step % 2 == 0 else (1024, 20000)
-        N.check(lib.b200cnn_comm_emulate_allreduce_sgd(world, ptrs, flat, off, cnt, 0.5, code, par, 3, C.c_void_p(seq.data_ptr()), st), "emulate")
+        slot = (0, 64, 0, 64 + 61)[step]  # both flag channels of one region, interleaved; the last one ends at slot 127
+        N.check(lib.b200cnn_comm_emulate_allreduce_sgd_slot(world, ptrs, flat, off, cnt, 0.5, code, par, 3, slot,
+                                                            C.c_void_p(seq.data_ptr()), st), "emulate")
         torch.cuda.synchronize()
         assert int(seq[world * 128]) == 0, "a virtual rank timed out waiting for a peer"
         total = torch.zeros(flat, dtype=torch.float64, device="cuda")
