@@ -14,6 +14,7 @@
 // Ordering: flag words carry a per-block sequence number that only ever grows; a rank publishes with
 // st.release.sys after a CTA barrier and waits with ld.acquire.sys.  Waits give up after ~2 s and
 // raise an error flag rather than hanging the GPU.
+#include <cstdlib>
 #include <new>
 
 #include "../cuda/common.cuh"
@@ -225,9 +226,11 @@ allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ l
     if (threadIdx.x == 0) *seq_slot = seq;
 }
 
-int pick_blocks(size_t n4, int max_blocks) {
+int pick_blocks(size_t n4, int max_blocks, int per_thread = 4) {
     // ~4 float4 per thread per block before adding blocks: launch + flag latency dominates small slices.
-    size_t b = (n4 + size_t(kCommThreads) * 4 - 1) / (size_t(kCommThreads) * 4);
+    // (per_thread = 1 for a slice on the critical path: every extra trip of the loop is one more NVLink round trip,
+    //  while extra blocks exchange their flags in parallel.)
+    size_t b = (n4 + size_t(kCommThreads) * per_thread - 1) / (size_t(kCommThreads) * per_thread);
     if (max_blocks <= 0 || max_blocks > kMaxBlocks) max_blocks = kMaxBlocks;
     if (b < 1) b = 1;
     if (b > size_t(max_blocks)) b = size_t(max_blocks);
@@ -293,13 +296,13 @@ int launch(const CommView& v, int ranks_y, size_t off4, size_t n4, const float* 
 }
 
 int enqueue(b200cnn_comm* c, size_t offset, size_t count, const float* lr_dev, float lr, int algo, int parity, int op,
-            int root, int max_blocks, cudaStream_t st, int block_base = 0) {
+            int root, int max_blocks, cudaStream_t st, int block_base = 0, int per_thread = 4) {
     if ((offset | count) & 3) return set_error(kInvalidValue, "comm: offset and count must be multiples of 4 floats");
     if (offset + count > c->flat_floats) return set_error(kInvalidValue, "comm: slice [%zu, %zu) outside the %zu-float buffer", offset, offset + count, c->flat_floats);
     if (parity != 0 && parity != 1) return set_error(kInvalidValue, "comm: parity must be 0 or 1");
     algo = resolve_algo(c, algo, count, op);
     const size_t n4 = count / 4;
-    int blocks = pick_blocks(n4, max_blocks);
+    int blocks = pick_blocks(n4, max_blocks, per_thread);
     if (op == kOpReduceOnly && algo == B200CNN_ALGO_ONE_SHOT) {
         // registers hold the results across the barrier: make sure 4 per thread is enough
         const size_t need = (n4 + size_t(kCommThreads) * 4 - 1) / (size_t(kCommThreads) * 4);
@@ -437,7 +440,16 @@ int comm_allreduce_sgd_slice(b200cnn_comm* c, size_t offset, size_t count, const
 // kernel that comm_allreduce_sgd_slice put on the communicator's own stream.  Used for the last bucket of a step,
 // which sits on the critical path.
 int comm_allreduce_sgd_inline(b200cnn_comm* c, size_t offset, size_t count, const float* lr_dev, cudaStream_t st) {
-    return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, 16, st, kMaxBlocks / 2);
+    // A small slice here is pure latency: one flag exchange (one-shot) with one float4 per thread beats the two
+    // exchanges of two-shot / NVLS at every world size.  B200CNN_COMM_TAIL_ALGO (1 one-shot, 2 two-shot, 3 NVLS)
+    // overrides the choice for experiments.
+    static const int forced = [] {
+        const char* s = std::getenv("B200CNN_COMM_TAIL_ALGO");
+        return s ? std::atoi(s) : 0;
+    }();
+    int algo = forced > 0 ? forced : B200CNN_ALGO_AUTO;
+    if (forced <= 0 && count * sizeof(float) <= (32u << 10)) algo = B200CNN_ALGO_ONE_SHOT;
+    return enqueue(c, offset, count, lr_dev, 0.0f, algo, c->parity, kOpSgd, 0, 16, st, kMaxBlocks / 2, /*per_thread=*/1);
 }
 
 int comm_join(b200cnn_comm* c, cudaStream_t st) {
