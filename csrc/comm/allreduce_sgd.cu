@@ -129,6 +129,43 @@ __device__ __forceinline__ float4 reduce_ranks(const float4* const* g, int world
     }
 }
 
+// Elements per thread per trip: a trip costs one NVLink round trip whatever it carries, so small worlds put
+// several elements' loads in flight at once (U x W = 8 peer loads per thread per trip).
+template <int W>
+struct Unroll {
+    static constexpr int value = (W == 1 || W == 2) ? 4 : (W == 4 ? 2 : 1);
+};
+
+// s[u] = sum over ranks (rank order) of element i + u * stride, for the u with i + u * stride < end.
+template <int W, int U>
+__device__ __forceinline__ void reduce_ranks_batch(const float4* const* g, int world, size_t i, size_t stride, size_t end,
+                                                   float4 (&s)[U]) {
+    if (W > 0 && U > 1) {
+        float4 vals[U][W > 0 ? W : 1];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const size_t idx = i + size_t(u) * stride;
+            if (idx < end) {
+#pragma unroll
+                for (int k = 0; k < W; k++) vals[u][k] = ld_peer(g[k] + idx);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (i + size_t(u) * stride < end) {
+                float4 acc = vals[u][0];
+#pragma unroll
+                for (int k = 1; k < W; k++) acc = add4(acc, vals[u][k]);
+                s[u] = acc;
+            }
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (i + size_t(u) * stride < end) s[u] = reduce_ranks<W>(g, world, i + size_t(u) * stride);
+    }
+}
+
 template <int W>
 __global__ void __launch_bounds__(kCommThreads)
 allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ lr_dev, float lr_imm, int algo,
@@ -162,14 +199,23 @@ allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ l
         need_exit_barrier = true;  // root must not change its parameters before everyone has read them
     } else if (algo == B200CNN_ALGO_ONE_SHOT) {
         if (op == kOpSgd) {
-            for (size_t i = tid; i < n4; i += nthreads) {
-                const float4 s = reduce_ranks<W>(g, world, i);
-                float4 w = w_local[i];
-                w.x -= lr * s.x;
-                w.y -= lr * s.y;
-                w.z -= lr * s.z;
-                w.w -= lr * s.w;
-                w_local[i] = w;
+            constexpr int U = Unroll<W>::value;
+            for (size_t i = tid; i < n4; i += nthreads * U) {
+                float4 s[U], w[U];
+#pragma unroll
+                for (int u = 0; u < U; u++)
+                    if (i + u * nthreads < n4) w[u] = w_local[i + u * nthreads];
+                reduce_ranks_batch<W, U>(g, world, i, nthreads, n4, s);
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    if (i + u * nthreads < n4) {
+                        w[u].x -= lr * s[u].x;
+                        w[u].y -= lr * s[u].y;
+                        w[u].z -= lr * s[u].z;
+                        w[u].w -= lr * s[u].w;
+                        w_local[i + u * nthreads] = w[u];
+                    }
+                }
             }
         } else {
             // In-place all-reduce: peers are still reading this rank's slice, so results may only
@@ -204,20 +250,32 @@ allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ l
                 }
             }
         } else {
-            for (size_t i = lo + tid; i < hi; i += nthreads) {
-                const float4 s = reduce_ranks<W>(g, world, i);
-                float4 out = s;
+            constexpr int U = Unroll<W>::value;
+            const size_t dst_off = (op == kOpSgd) ? v.params_off : v.grads_off[parity];
+            for (size_t i = lo + tid; i < hi; i += nthreads * U) {
+                float4 s[U], out[U];
                 if (op == kOpSgd) {
-                    out = w_local[i];
-                    out.x -= lr * s.x;
-                    out.y -= lr * s.y;
-                    out.z -= lr * s.z;
-                    out.w -= lr * s.w;
-                }
-                const size_t dst_off = (op == kOpSgd) ? v.params_off : v.grads_off[parity];
 #pragma unroll
-                for (int k = 0; k < kMaxRanks; k++)
-                    if (k < world) st_peer(reinterpret_cast<float4*>(v.region[k] + dst_off) + off4 + i, out);
+                    for (int u = 0; u < U; u++)
+                        if (i + u * nthreads < hi) out[u] = w_local[i + u * nthreads];
+                }
+                reduce_ranks_batch<W, U>(g, world, i, nthreads, hi, s);
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    const size_t idx = i + u * nthreads;
+                    if (idx >= hi) continue;
+                    if (op == kOpSgd) {
+                        out[u].x -= lr * s[u].x;
+                        out[u].y -= lr * s[u].y;
+                        out[u].z -= lr * s[u].z;
+                        out[u].w -= lr * s[u].w;
+                    } else {
+                        out[u] = s[u];
+                    }
+#pragma unroll
+                    for (int k = 0; k < kMaxRanks; k++)
+                        if (k < world) st_peer(reinterpret_cast<float4*>(v.region[k] + dst_off) + off4 + idx, out[u]);
+                }
             }
         }
         need_exit_barrier = true;  // all shards must have landed everywhere before anyone moves on
@@ -433,7 +491,13 @@ int comm_allreduce_sgd_slice(b200cnn_comm* c, size_t offset, size_t count, const
     B200CNN_CUDA(cudaEventRecord(c->ev_fork, after));
     B200CNN_CUDA(cudaStreamWaitEvent(c->stream, c->ev_fork, 0));
     c->forked = true;
-    return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, 16, c->stream);
+    // Few blocks: the kernel shares the GPU with the rest of backward.  (B200CNN_COMM_BLOCKS overrides, <= 64.)
+    static const int max_blocks = [] {
+        const char* s = std::getenv("B200CNN_COMM_BLOCKS");
+        const int v = s ? std::atoi(s) : 16;
+        return v < 1 ? 1 : v > kMaxBlocks / 2 ? kMaxBlocks / 2 : v;
+    }();
+    return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, max_blocks, c->stream);
 }
 
 // Same operation enqueued directly on `st` (no stream hop), on the second flag channel so it may overlap a
