@@ -48,6 +48,12 @@ bool tc_conv3x3s2_bwd_data_supported(const b200cnn_conv_shape* s);
 int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
                           float* dx_nhwc, const b200cnn_conv_shape* s, cudaStream_t st);
 
+// tc_conv_wgrad.cu: split-K implicit-GEMM weight gradient of the 16->32 channel 3x3/s2 convolution (14x14 -> 7x7)
+bool tc_conv3x3s2_bwd_weight_supported(const b200cnn_conv_shape* s);
+size_t tc_conv3x3s2_bwd_weight_scratch_floats(int n);
+int tc_conv3x3s2_bwd_weight(const float* x_nhwc, const float* dz, int dz_is_chw, float* dw, float* db, int accumulate,
+                            float* part, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st);
+
 // conv_nhwc.cu / conv.cu
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
 int nhwc_bwd_weight_chunks(int n, int* spb_out);

@@ -8,6 +8,8 @@
 // Replaces the weight half of Layer_feedBack_conv (/root/reference/cnn.c:236, :242).
 #include <algorithm>
 
+#include <cstdlib>
+
 #include "backend.cuh"
 #include "common.cuh"
 
@@ -273,6 +275,16 @@ int nhwc_bwd_weight_chunks(int n, int* spb_out) {
     return ceil_div(n, spb);
 }
 
+// The tcgen05 weight-gradient kernel is used when the backend allows it (B200CNN_TC_WGRAD=0 keeps the CUDA-core
+// kernel, for A/B timing).
+static bool tc_wgrad_enabled() {
+    static const bool env_on = [] {
+        const char* v = getenv("B200CNN_TC_WGRAD");
+        return !(v && v[0] == '0');
+    }();
+    return env_on && current_backend() != B200CNN_BACKEND_SIMT;
+}
+
 // x: NHWC float (or [n][h][w] uint8/float when c == 1); dz: NHWC, or CHW when dz_chw (c > 1 only).
 // dw OIHW, db [oc].  partials: chunks*(nw+oc) floats.
 // counter: one zero-initialised word used by the single-channel kernel's "last block reduces" step (it resets
@@ -306,6 +318,11 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
             B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(kC1Threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f, dw, db, accumulate, counter, sgd_w, sgd_b, lr_dev));
         }
+    } else if (tc_wgrad_enabled() && !x_is_u8 && tc_conv3x3s2_bwd_weight_supported(s) &&
+               tc_conv3x3s2_bwd_weight_scratch_floats(s->n) <= size_t(chunks) * (nw + s->oc)) {
+        // tensor cores: split-K implicit GEMM, reduced through DSMEM + one partial per cluster; completion counter =
+        // header word 1 (word 0 belongs to the single-channel kernel)
+        return tc_conv3x3s2_bwd_weight(static_cast<const float*>(x), dz, dz_chw, dw, db, accumulate, partials, header + 1, s, st);
     } else {
         const int work = (s->oc / 4) * (s->c / 4) * kk;
         const int threads = ((work + 31) / 32) * 32;

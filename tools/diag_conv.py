@@ -24,7 +24,7 @@ for (n, h, oc, s, pad) in [(2, 14, 32, 2, 1), (256, 14, 32, 2, 1), (5, 14, 16, 2
     torch.cuda.synchronize()
     want = torch.relu(F.conv2d(x, w, b, s, pad)).reshape(n, -1)
     stat(f"fwd n{n} h{h} oc{oc} s{s} p{pad} rc={rc} {lib.b200cnn_last_error().decode()[:30]}", y[:, :oc * oh * oh], want)
-for n in (2, 256, 7):
+for n in (2, 256, 7, 72):
     torch.manual_seed(1)
     dz = torch.randn(n, 32, 7, 7, device="cuda"); w = torch.randn(32, 16, 3, 3, device="cuda") * 0.1
     a1 = torch.randn(n, 16, 14, 14, device="cuda")
