@@ -52,7 +52,7 @@ int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const 
 bool tc_conv3x3s2_bwd_weight_supported(const b200cnn_conv_shape* s);
 size_t tc_conv3x3s2_bwd_weight_scratch_floats(int n);
 int tc_conv3x3s2_bwd_weight(const float* x_nhwc, const float* dz, int dz_is_chw, float* dw, float* db, int accumulate,
-                            float* part, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st);
+                            float* part, const b200cnn_conv_shape* s, cudaStream_t st);
 
 // conv_nhwc.cu / conv.cu
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);

@@ -320,9 +320,8 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         }
     } else if (tc_wgrad_enabled() && !x_is_u8 && tc_conv3x3s2_bwd_weight_supported(s) &&
                tc_conv3x3s2_bwd_weight_scratch_floats(s->n) <= size_t(chunks) * (nw + s->oc)) {
-        // tensor cores: split-K implicit GEMM, reduced through DSMEM + one partial per cluster; completion counter =
-        // header word 1 (word 0 belongs to the single-channel kernel)
-        return tc_conv3x3s2_bwd_weight(static_cast<const float*>(x), dz, dz_chw, dw, db, accumulate, partials, header + 1, s, st);
+        // tensor cores: split-K implicit GEMM + a small reduce kernel over the n/8 partial tiles
+        return tc_conv3x3s2_bwd_weight(static_cast<const float*>(x), dz, dz_chw, dw, db, accumulate, partials, s, st);
     } else {
         const int work = (s->oc / 4) * (s->c / 4) * kk;
         const int threads = ((work + 31) / 32) * 32;

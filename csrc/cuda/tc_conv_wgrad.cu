@@ -4,17 +4,21 @@
 // i.e. D[M = (kx, c)][N = oc] = sum_K A[K][M] * B[K][N] with K = output pixels, for each ky.  Both operands are
 // "MN-major" (the K index is the ROW of the staged tile), which is exactly what TMA delivers without any im2col:
 //   A  x is NHWC with 16 channels, so two horizontally adjacent pixels are 32 contiguous floats = one 128-byte
-//      row.  Seen as dims (32 floats, W/2 pairs, H, N) a box (32, 7, 13 walked with stride 2, 8 images) started
-//      at pair 0 / row ky-1 is [392 pixels][taps kx=1 | kx=2], and started at pair -1 it is [392 pixels]
+//      row.  Seen as dims (32 floats, W/2 pairs, H, N) a box (32, 7, 13 walked with stride 2, 4 images) started
+//      at pair 0 / row ky-1 is [196 pixels][taps kx=1 | kx=2], and started at pair -1 it is [196 pixels]
 //      [unused | tap kx=0]; out-of-bounds pairs / rows are the zero padding.  Two boxes = one 64-row M extent.
-//   B  dz [392 pixels][32 oc]: one TMA box when dz is NHWC; when it arrives CHW (what the FC layer above
-//      writes) the epilogue warps transpose it into the same swizzled tile while the A boxes are in flight.
-// 8 images per CTA = 392 K rows = 49 tcgen05.mma (M=128 of which 64 rows are used, N=32, K=8) into one TMEM
-// tile.  Grid (3 ky, 1, n/8) in clusters of 8 along z: the 7 peers ship their 64x32 partial tiles into the
-// leader's shared memory (DSMEM), the leader adds them in rank order and writes one partial per cluster; the
-// last leader to finish (device counter) adds the clusters' partials in index order and scatters dW / db in
-// the reference's OIHW layout.  Fixed summation order everywhere: results are run-to-run identical.
-// Bias gradient: column sums of B, carried in row 0 of the partial tile (an unused tap row).
+//   B  dz [196 pixels][32 oc]: one TMA box when dz is NHWC; when it arrives CHW (what the FC layer above
+//      writes) the epilogue warps repack it: coalesced float4 loads of one image into a 6 KB buffer, then a
+//      conflict-free shared -> shared transpose into the swizzled tile, the next image's loads already in flight.
+// A CTA owns 8 images and runs them as two phases of 4 (196 K rows + 4 zero rows = 25 tcgen05.mma of M=64, N=32,
+// K=8 each) through ONE set of tiles, so it needs 83 KB of shared memory and fits on an SM next to the CTAs of the
+// data-gradient kernel and of the first convolution's weight-gradient kernel that run at the same time.
+// Grid (3 ky, 1, n/8): every CTA stores its 64x32 partial tile, and a second small kernel (chained with
+// programmatic dependent launch) adds the n/8 partials in index order and scatters dW / db in the reference's
+// OIHW layout: fixed summation order, run-to-run identical results.  (Measured alternative, kept out: reducing
+// inside the kernel through DSMEM in clusters of 8 + a "last leader" pass cost 13 us of barriers, fences and
+// one-SM funnelling against ~3 us for the second kernel.)
+// Bias gradient: column sums of dz, carried in row 0 of the partial tile (an unused tap row).
 //
 // Replaces the weight half of Layer_feedBack_conv (/root/reference/cnn.c:236,242) for the second convolution.
 #include <cstdlib>
@@ -29,221 +33,182 @@ namespace {
 
 using namespace tc;
 
-constexpr int kWgThreads = 192;               // warp 0: TMA, warp 1: TMEM + MMA, warps 2-5: dz staging + epilogue
-constexpr int kIpc = 8;                       // images per CTA
+constexpr int kWgThreads = 192;               // warp 0: TMA, warp 1: TMEM + MMA, warps 2-5: dz repack + epilogue
+constexpr int kIpc = 8;                       // images per CTA ...
+constexpr int kPhaseImgs = 4;                 // ... in two phases of 4
 constexpr int kPix = 49;                      // 7 x 7 output pixels
-constexpr int kRows = kIpc * kPix;            // 392 K rows = 49 MMA steps of 8
-constexpr int kGroupBytes = kRows * 128;      // one [392][32 floats] tile
-constexpr int kCluster = 8;
+constexpr int kBoxRows = kPhaseImgs * kPix;   // 196 K rows written per phase
+constexpr int kSteps = (kBoxRows + 7) / 8;    // 25 MMA steps (rows 196..199 are zero)
+constexpr int kTileBytes = kSteps * 8 * 128;  // 25,600: one [200][32 floats] tile
+constexpr int kBoxBytes = kBoxRows * 128;
+constexpr int kImgFloats = 32 * kPix;         // one image of dz
 constexpr int kPartFloats = 64 * 32;          // partial tile: rows (kx+1)*16 + c, row 0 = bias gradient
 constexpr int kOC = 32, kC = 16;
-// The M=128 instruction shape reads four 32-float M groups kGroupBytes apart: the allocation must cover all
-// four even though only two hold data (groups 2 and 3 produce accumulator rows nobody reads).  The M=64 shape reads
-// two, so it fits next to other kernels' CTAs on the same SM.
-template <bool M64>
-constexpr size_t wg_smem() { return (M64 ? 3 : 4) * size_t(kGroupBytes) + 4 * 32 * 4 + 64 + 1024; }
-static_assert((kCluster - 1) * kPartFloats * 4 <= 2 * kGroupBytes, "peers' partial tiles reuse the A tiles");
+constexpr size_t kWgSmem = 3 * size_t(kTileBytes) + kImgFloats * 4 + 4 * 32 * 4 + 64 + 1024;
 
 struct WgradArgs {
-    const float* dz_chw;  // non-NULL: dz as [n][32][49]; NULL: NHWC through tmap_dz
-    float* part;          // [3][clusters][64][32]
-    unsigned* counter;    // zero before the first launch; resets itself
-    float* dw;            // OIHW [32][16][3][3]
-    float* db;            // [32]
-    int n, clusters, accumulate;
+    const float* dz_chw;   // non-NULL: dz as [n][32][49]
+    const float* dz_nhwc;  // non-NULL: dz as [n][49][32] (also behind tmap_dz)
+    float* part;           // [3][n/8][64][32]
+    float* dw;             // OIHW [32][16][3][3]
+    float* db;             // [32]
+    int n;
+    long long* dbg;        // instrumentation (B200CNN_WG_DEBUG=1): clock64 stamps of the cluster leaders, [ky*4+z][16] for z < 4
 };
 
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
+#define WG_STAMP(i) do { if (a.dbg && blockIdx.z < 4) a.dbg[(ky * 4 + blockIdx.z) * 16 + (i)] = clock64(); } while (0)
 __device__ __forceinline__ void epilogue_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <bool M64>
 __global__ void __launch_bounds__(kWgThreads, 1)
 tc_conv3x3s2_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_dz,
                                WgradArgs a) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* a_tile = smem;                        // 2 groups: [unused | kx0], [kx1 | kx2]
-    uint8_t* b_tile = smem + 2 * kGroupBytes;      // dz
-    float* red = reinterpret_cast<float*>(smem);   // leader, after the MMAs: [7][64][32] partial tiles of the peers
-    float* dbp = reinterpret_cast<float*>(smem + (M64 ? 3 : 4) * kGroupBytes);  // [4 warps][32] bias-gradient partials
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(dbp + 4 * 32);
-    uint64_t* tmem_full_bar = full_bar + 1;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-    uint32_t* last_flag = tmem_slot + 1;
+    uint8_t* b_tile = smem + 2 * kTileBytes;       // dz
+    float* raw = reinterpret_cast<float*>(smem + 3 * kTileBytes);  // one CHW image of dz
+    float* dbp = raw + kImgFloats;                 // [4 warps][32] bias-gradient partials
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(dbp + 4 * 32);  // TMA boxes of a phase have landed
+    uint64_t* b_bar = full_bar + 1;                // repacked dz of a phase is in place (4 warps)
+    uint64_t* mma_bar = full_bar + 2;              // phase-0 MMAs have finished reading the tiles
+    uint64_t* tmem_full_bar = full_bar + 3;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(full_bar + 4);
 
     const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
     const int ky = blockIdx.x;
-    const int rank = int(cluster_ctarank());
-    const int cl = int(blockIdx.z) / kCluster;
     const int n0 = int(blockIdx.z) * kIpc;
-    const bool has = n0 < a.n;  // (n is a multiple of 8; trailing CTAs of the last cluster may have nothing)
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_x);
         if (!a.dz_chw) prefetch_tmap(&tmap_dz);
         mbar_init(full_bar, 1);
+        mbar_init(b_bar, 4);
+        mbar_init(mma_bar, 1);
         mbar_init(tmem_full_bar, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<32>(tmem_slot);
+    // K rows 196..199 of every tile are never written by TMA or the repack: zero them once.
+    for (int i = threadIdx.x; i < 3 * 128; i += kWgThreads)
+        *reinterpret_cast<float*>(smem + (i / 128) * kTileBytes + kBoxBytes + (i % 128) * 4) = 0.0f;
+    fence_proxy_async_smem();
     tcgen05_fence_before();
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) WG_STAMP(0);
     pdl_wait();
     pdl_launch_dependents();
+    if (threadIdx.x == 0) WG_STAMP(1);
 
     if (warp == 0) {
-        if (lane == 0 && has) {
-            mbar_arrive_expect_tx(full_bar, uint32_t((a.dz_chw ? 2 : 3) * kGroupBytes));
-            tma_load_4d(a_tile, &tmap_x, full_bar, 0, -1, ky - 1, n0);
-            tma_load_4d(a_tile + kGroupBytes, &tmap_x, full_bar, 0, 0, ky - 1, n0);
-            if (!a.dz_chw) tma_load_4d(b_tile, &tmap_dz, full_bar, 0, 0, 0, n0);
-        }
-    } else if (warp >= 2 && a.dz_chw) {
-        // CHW -> [pixel][oc] rows of 128 bytes in the 128B-swizzle-with-32B-atoms layout (32-byte chunk index
-        // ^= row & 3).  Lane = oc: the 32 lanes of a store hit 32 different banks; each lane reads its 49
-        // contiguous floats of (image, oc) with all loads in flight.
-        const int w = warp - 2, oc = lane;
-        float s = 0.0f;
-        if (has) {
-#pragma unroll 1
-            for (int gi = 0; gi < kIpc / 4; gi++) {
-                const int g = w + 4 * gi;
-                const float* src = a.dz_chw + (size_t(n0 + g) * kOC + oc) * kPix;
-                float v[kPix];
-#pragma unroll
-                for (int p = 0; p < kPix; p++) v[p] = __ldg(src + p);
-#pragma unroll
-                for (int p = 0; p < kPix; p++) {
-                    const int r = g * kPix + p;
-                    *reinterpret_cast<float*>(b_tile + r * 128 + (((oc >> 3) ^ (r & 3)) << 5) + (oc & 7) * 4) = v[p];
-                    s += v[p];
-                }
+        if (lane == 0) {
+            for (int h = 0; h < 2; h++) {
+                if (h == 1) { mbar_wait(mma_bar, 0); WG_STAMP(4); }
+                mbar_arrive_expect_tx(full_bar, uint32_t((a.dz_chw ? 2 : 3) * kBoxBytes));
+                tma_load_4d(a_tile, &tmap_x, full_bar, 0, -1, ky - 1, n0 + kPhaseImgs * h);
+                tma_load_4d(a_tile + kTileBytes, &tmap_x, full_bar, 0, 0, ky - 1, n0 + kPhaseImgs * h);
+                if (!a.dz_chw) tma_load_4d(b_tile, &tmap_dz, full_bar, 0, 0, 0, n0 + kPhaseImgs * h);
             }
-            fence_proxy_async_smem();
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_tf32(64, kOC, true, true);
+            const uint32_t a_addr = smem_u32(a_tile), b_addr = smem_u32(b_tile);
+            for (int h = 0; h < 2; h++) {
+                mbar_wait(full_bar, uint32_t(h));
+                WG_STAMP(h == 0 ? 2 : 5);
+                if (a.dz_chw) mbar_wait(b_bar, uint32_t(h));
+                WG_STAMP(h == 0 ? 3 : 6);
+                tcgen05_fence_after();
+#pragma unroll 5
+                for (int kk = 0; kk < kSteps; kk++) {
+                    // M-major A: the two 32-float groups are kTileBytes apart; 8 K rows further = 1024 bytes.
+                    const uint64_t da = make_smem_desc(a_addr + kk * 1024, kTileBytes, 512, kSw128Base32);
+                    const uint64_t db = make_smem_desc(b_addr + kk * 1024, 4096, 512, kSw128Base32);
+                    umma_tf32(tmem_base, da, db, idesc, (h | kk) != 0);
+                }
+                umma_commit(h == 0 ? mma_bar : tmem_full_bar);
+            }
+        }
+    } else {
+        const int w = warp - 2, oc = lane, t = threadIdx.x - 64;
+        float s = 0.0f;
+        if (a.dz_chw) {
+            // One image at a time: coalesced float4 loads (the next image's already in flight) -> raw[oc][49] ->
+            // B[pixel][oc] rows of 128 bytes in the 128B-swizzle-with-32B-atoms layout (32-byte chunk ^= row & 3).
+            // Lane = oc on both sides of the transpose: raw reads are 49 floats apart (odd: no bank conflict), tile
+            // writes hit 32 different banks.
+            constexpr int kQuads = kImgFloats / 4;  // 392
+            float4 cur[4], nxt[4];
+            const float4* src0 = reinterpret_cast<const float4*>(a.dz_chw + size_t(n0) * kImgFloats);
+#pragma unroll
+            for (int u = 0; u < 4; u++) cur[u] = (t + 128 * u < kQuads) ? __ldg(src0 + t + 128 * u) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+            for (int i = 0; i < kIpc; i++) {
+                const int g = i % kPhaseImgs;
+                if (i == kPhaseImgs) mbar_wait(mma_bar, 0);  // phase-0 MMAs are done with the tile
+                if (i + 1 < kIpc) {
+                    const float4* src = src0 + size_t(i + 1) * kQuads;
+#pragma unroll
+                    for (int u = 0; u < 4; u++) nxt[u] = (t + 128 * u < kQuads) ? __ldg(src + t + 128 * u) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if (t + 128 * u < kQuads) reinterpret_cast<float4*>(raw)[t + 128 * u] = cur[u];
+                epilogue_bar_sync();
+#pragma unroll
+                for (int pp = 0; pp < 13; pp++) {
+                    const int p = w + 4 * pp;
+                    if (p < kPix) {
+                        const float v = raw[oc * kPix + p];
+                        const int r = g * kPix + p;
+                        *reinterpret_cast<float*>(b_tile + r * 128 + (((oc >> 3) ^ (r & 3)) << 5) + (oc & 7) * 4) = v;
+                        s += v;
+                    }
+                }
+                epilogue_bar_sync();  // raw may be overwritten
+                if (g == kPhaseImgs - 1) {
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(b_bar);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) cur[u] = nxt[u];
+            }
+        } else if (ky == 0) {
+            // NHWC: bias gradient straight from global memory (coalesced rows of 32 oc)
+            const float* src = a.dz_nhwc + size_t(n0) * kImgFloats + oc;
+#pragma unroll 14
+            for (int r = w * (kIpc * kPix / 4); r < (w + 1) * (kIpc * kPix / 4); r++) s += __ldg(src + size_t(r) * kOC);
         }
         dbp[w * 32 + oc] = s;
     }
-    __syncthreads();
-
-    if (warp == 1) {
-        if (lane == 0 && has) {
-            constexpr uint32_t idesc = make_idesc_tf32(M64 ? 64 : 128, kOC, true, true);
-            mbar_wait(full_bar, 0);
-            tcgen05_fence_after();
-            const uint32_t a_addr = smem_u32(a_tile), b_addr = smem_u32(b_tile);
-#pragma unroll 7
-            for (int kk = 0; kk < kRows / 8; kk++) {
-                // M-major A: 32-float groups kGroupBytes apart (groups 2, 3 of the M=128 shape read whatever follows:
-                // their accumulator rows 64..127 are never looked at).  8 K rows further = 1024 bytes.
-                const uint64_t da = make_smem_desc(a_addr + kk * 1024, kGroupBytes, 512, kSw128Base32);
-                const uint64_t db = make_smem_desc(b_addr + kk * 1024, 4096, 512, kSw128Base32);
-                umma_tf32(tmem_base, da, db, idesc, kk != 0);
-            }
-            umma_commit(tmem_full_bar);
-        }
-    }
-    float v[32];
-    const int q = warp & 3;
-    // Accumulator row of this thread.  M=128: row = TMEM lane (rows 0..63 live in lane quarters 0 and 1).
-    // M=64: each lane quarter holds 16 rows in its first 16 lanes.
-    const int m = M64 ? 16 * q + lane : 32 * q + lane;
-    const bool ld_warp = warp >= 2 && (M64 || q < 2);
-    const bool epi = ld_warp && (!M64 || lane < 16);
+    // Accumulator row of this thread: with M=64 each TMEM lane quarter holds 16 rows in its first 16 lanes.
     if (warp >= 2) {
-        if (!a.dz_chw) {
-            // NHWC: bias gradient = column sums of the staged dz tile (only the ky = 0 CTAs report it)
-            const int w = warp - 2, oc = lane;
-            float s = 0.0f;
-            if (has && ky == 0) {
-                mbar_wait(full_bar, 0);
-#pragma unroll 14
-                for (int r = w * (kRows / 4); r < (w + 1) * (kRows / 4); r++)
-                    s += *reinterpret_cast<const float*>(b_tile + r * 128 + (((oc >> 3) ^ (r & 3)) << 5) + (oc & 7) * 4);
-            }
-            dbp[w * 32 + oc] = s;
-        }
+        const int q = warp & 3;
+        const int m = 16 * q + lane;
         epilogue_bar_sync();  // dbp complete
-        if (ld_warp) {
-            if (has) {
-                mbar_wait(tmem_full_bar, 0);
-                tcgen05_fence_after();
-                float t[16];
-                tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16), t);
+        mbar_wait(tmem_full_bar, 0);
+        if (threadIdx.x == 64) WG_STAMP(7);
+        tcgen05_fence_after();
+        float v[32], t16[16];
+        tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16), t16);
 #pragma unroll
-                for (int i = 0; i < 16; i++) v[i] = t[i];
-                tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + 16u, t);
+        for (int i = 0; i < 16; i++) v[i] = t16[i];
+        tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + 16u, t16);
 #pragma unroll
-                for (int i = 0; i < 16; i++) v[16 + i] = t[i];
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; i++) v[i] = 0.0f;
-            }
-            if (epi && m == 0) {
+        for (int i = 0; i < 16; i++) v[16 + i] = t16[i];
+        if (lane < 16) {
+            if (m == 0) {  // row 0 (an unused tap row) carries this CTA's bias-gradient partial
 #pragma unroll
                 for (int i = 0; i < 32; i++) v[i] = (dbp[i] + dbp[32 + i]) + (dbp[64 + i] + dbp[96 + i]);
             }
-        }
-    }
-    // Everyone's MMAs have finished reading shared memory: the leader's A tiles may now receive the partial tiles.
-    tcgen05_fence_before();
-    cluster_sync_all();
-    if (epi && rank != 0) {
-        const uint32_t dst = map_to_cluster_rank(smem_u32(red + (size_t(rank - 1) * 64 + m) * 32), 0);
-#pragma unroll
-        for (int i = 0; i < 8; i++) st_cluster_f32x4(dst + 16 * i, v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-    }
-    cluster_sync_all();
-    if (rank == 0) {
-        if (epi) {
-#pragma unroll 1
-            for (int p = 0; p < kCluster - 1; p++) {
-                const float4* pr = reinterpret_cast<const float4*>(red + (size_t(p) * 64 + m) * 32);
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    const float4 t4 = pr[i];
-                    v[4 * i] += t4.x; v[4 * i + 1] += t4.y; v[4 * i + 2] += t4.z; v[4 * i + 3] += t4.w;
-                }
-            }
-            float4* out = reinterpret_cast<float4*>(a.part + ((size_t(ky) * a.clusters + cl) * 64 + m) * 32);
+            float4* out = reinterpret_cast<float4*>(a.part + ((size_t(ky) * gridDim.z + blockIdx.z) * 64 + m) * 32);
 #pragma unroll
             for (int i = 0; i < 8; i++) out[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-            __threadfence();
         }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            const unsigned total = 3u * unsigned(a.clusters);
-            *last_flag = (atomicAdd(a.counter, 1u) == total - 1) ? 1u : 0u;
-        }
-        __syncthreads();
-        if (*last_flag) {
-            __threadfence();
-            // (ky, row 16..63, 4 oc) items + the 8 bias items of (ky 0, row 0)
-            const int items = 3 * 48 * 8 + 8;
-            for (int t = threadIdx.x; t < items; t += kWgThreads) {
-                const bool is_bias = t >= 3 * 48 * 8;
-                const int tt = is_bias ? t - 3 * 48 * 8 : t;
-                const int kyy = is_bias ? 0 : tt / 384, row = is_bias ? 0 : 16 + (tt % 384) / 8, oc4 = tt % 8;
-                float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int c2 = 0; c2 < a.clusters; c2++) {
-                    const float4 p4 = __ldcg(reinterpret_cast<const float4*>(a.part + ((size_t(kyy) * a.clusters + c2) * 64 + row) * 32) + oc4);
-                    s.x += p4.x; s.y += p4.y; s.z += p4.z; s.w += p4.w;
-                }
-                const float sv[4] = {s.x, s.y, s.z, s.w};
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int oc = oc4 * 4 + i;
-                    float* dst = is_bias ? a.db + oc : a.dw + (size_t(oc) * kC + (row & 15)) * 9 + kyy * 3 + (row / 16 - 1);
-                    *dst = a.accumulate ? *dst + sv[i] : sv[i];
-                }
-            }
-            if (threadIdx.x == 0) *a.counter = 0;
-        }
+        if (threadIdx.x == 64) WG_STAMP(8);
     }
     tcgen05_fence_before();
     __syncthreads();
@@ -253,7 +218,42 @@ tc_conv3x3s2_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const
     }
 }
 
+// dW / db = sum over the K splits of the partial tiles, in split order (fixed: results are run-to-run identical).
+// One thread per 4 output channels of one (ky, kx, c) row; all of a thread's loads are independent.
+__global__ void __launch_bounds__(128)
+wgrad_reduce_kernel(const float* __restrict__ part, int splits, float* __restrict__ dw, float* __restrict__ db, int accumulate) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    constexpr int kItems = 3 * 48 * 8;  // + 8 bias items of (ky 0, row 0)
+    if (t >= kItems + 8) return;
+    const bool is_bias = t >= kItems;
+    const int tt = is_bias ? t - kItems : t;
+    const int ky = is_bias ? 0 : tt / 384, row = is_bias ? 0 : 16 + (tt % 384) / 8, oc4 = tt % 8;
+    const float4* src = reinterpret_cast<const float4*>(part + (size_t(ky) * splits * 64 + row) * 32) + oc4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+    for (int z = 0; z < splits; z++) {
+        const float4 p4 = __ldcg(src + size_t(z) * (64 * 32 / 4));
+        s.x += p4.x; s.y += p4.y; s.z += p4.z; s.w += p4.w;
+    }
+    const float sv[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int oc = oc4 * 4 + i;
+        float* dst = is_bias ? db + oc : dw + (size_t(oc) * kC + (row & 15)) * 9 + ky * 3 + (row / 16 - 1);
+        *dst = accumulate ? *dst + sv[i] : sv[i];
+    }
+}
+
 }  // namespace
+
+static long long* g_wg_dbg = nullptr;
+// Instrumentation read-back (tools/diag_wgrad.py): 16 clock64 stamps per cluster leader of the last launch.
+extern "C" int b200cnn_debug_wgrad_stamps(long long* out, int count) {
+    if (!g_wg_dbg || count > 64 * 16) return 1;
+    return cudaMemcpy(out, g_wg_dbg, size_t(count) * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 2;
+}
 
 bool tc_conv3x3s2_bwd_weight_supported(const b200cnn_conv_shape* s) {
     return s->k == 3 && s->stride == 2 && s->pad == 1 && s->c == kC && s->oc == kOC && s->oh == 7 && s->ow == 7 && s->h == 14 &&
@@ -261,20 +261,19 @@ bool tc_conv3x3s2_bwd_weight_supported(const b200cnn_conv_shape* s) {
 }
 
 size_t tc_conv3x3s2_bwd_weight_scratch_floats(int n) {
-    return size_t(3) * size_t(ceil_div(n, kIpc * kCluster)) * kPartFloats;
+    return size_t(3) * size_t(ceil_div(n, kIpc)) * kPartFloats;
 }
 
 // x: NHWC [n][14][14][16]; dz: NHWC [n][7][7][32] or CHW [n][32][7][7]; part: scratch_floats(n) floats;
-// counter: one zero-initialised word (the kernel leaves it zero).
 int tc_conv3x3s2_bwd_weight(const float* x_nhwc, const float* dz, int dz_is_chw, float* dw, float* db, int accumulate,
-                            float* part, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st) {
+                            float* part, const b200cnn_conv_shape* s, cudaStream_t st) {
     if (!tc_conv3x3s2_bwd_weight_supported(s)) return set_error(kInvalidValue, "tc_conv3x3s2_bwd_weight: unsupported shape");
     CUtensorMap tmx, tmdz;
     {
         // pairs of horizontally adjacent pixels: (32 floats, W/2, H, N)
         const uint64_t dims[4] = {32, uint64_t(s->w / 2), uint64_t(s->h), uint64_t(s->n)};
         const uint64_t strides[4] = {0, 128, uint64_t(s->w) * kC * 4, uint64_t(s->h) * s->w * kC * 4};
-        const uint32_t box[4] = {32, 7, 13, uint32_t(kIpc)};
+        const uint32_t box[4] = {32, 7, 13, uint32_t(kPhaseImgs)};
         const uint32_t estr[4] = {1, 1, 2, 1};
         if (int rc = encode_tmap_f32(&tmx, x_nhwc, 4, dims, strides, box, estr, kTmaSw128Atom32)) return rc;
     }
@@ -283,26 +282,26 @@ int tc_conv3x3s2_bwd_weight(const float* x_nhwc, const float* dz, int dz_is_chw,
         const float* base = dz_is_chw ? x_nhwc : dz;
         const uint64_t dims[4] = {32, 7, 7, uint64_t(s->n)};
         const uint64_t strides[4] = {0, 128, 7 * 128, 49 * 128};
-        const uint32_t box[4] = {32, 7, 7, uint32_t(kIpc)};
+        const uint32_t box[4] = {32, 7, 7, uint32_t(kPhaseImgs)};
         if (int rc = encode_tmap_f32(&tmdz, base, 4, dims, strides, box, nullptr, kTmaSw128Atom32)) return rc;
     }
-    const int clusters = ceil_div(s->n, kIpc * kCluster);
-    WgradArgs a{dz_is_chw ? dz : nullptr, part, counter, dw, db, s->n, clusters, accumulate};
-    static const bool m64 = [] {
-        const char* v = getenv("B200CNN_WGRAD_M64");
-        return !(v && v[0] == '0');  // default: the M=64 shape (smaller footprint); 0 = M=128
+    const int splits = s->n / kIpc;
+    static long long* dbg = [] {
+        long long* p = nullptr;
+        const char* v = getenv("B200CNN_WG_DEBUG");
+        if (v && v[0] == '1' && cudaMalloc(&p, 64 * 16 * sizeof(long long)) == cudaSuccess) cudaMemset(p, 0, 64 * 16 * sizeof(long long));
+        return p;
     }();
+    g_wg_dbg = dbg;
+    WgradArgs a{dz_is_chw ? dz : nullptr, dz_is_chw ? nullptr : dz, part, dw, db, s->n, dbg};
+    auto kern = tc_conv3x3s2_bwd_weight_kernel;
     static bool configured = false;
     if (!configured) {
-        B200CNN_CUDA(cudaFuncSetAttribute(tc_conv3x3s2_bwd_weight_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wg_smem<true>())));
-        B200CNN_CUDA(cudaFuncSetAttribute(tc_conv3x3s2_bwd_weight_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(wg_smem<false>())));
+        B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWgSmem)));
         configured = true;
     }
-    const dim3 grid(3, 1, clusters * kCluster);
-    if (m64)
-        B200CNN_CUDA(launch_kernel_cluster(tc_conv3x3s2_bwd_weight_kernel<true>, grid, dim3(kWgThreads), wg_smem<true>(), st, kCluster, tmx, tmdz, a));
-    else
-        B200CNN_CUDA(launch_kernel_cluster(tc_conv3x3s2_bwd_weight_kernel<false>, grid, dim3(kWgThreads), wg_smem<false>(), st, kCluster, tmx, tmdz, a));
+    B200CNN_CUDA(launch_kernel(kern, dim3(3, 1, splits), dim3(kWgThreads), kWgSmem, st, tmx, tmdz, a));
+    B200CNN_CUDA(launch_kernel(wgrad_reduce_kernel, dim3(ceil_div(3 * 48 * 8 + 8, 128)), dim3(128), 0, st, static_cast<const float*>(part), splits, dw, db, accumulate));
     B200CNN_CHECK_LAUNCH("tc_conv3x3s2_bwd_weight");
     return 0;
 }

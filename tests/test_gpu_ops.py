@@ -249,3 +249,39 @@ def test_fused_head_kernel(shape):
     got = met.cpu().numpy()
     assert got[3] == m and got[2] == float((rp.argmax(1) == lab.long()).sum())
     assert got[0] == pytest.approx(float(-torch.log(rp[torch.arange(m), lab.long()]).sum()), rel=2e-3)
+
+
+@pytest.mark.parametrize("n", [8, 72, 256, 20])
+@pytest.mark.parametrize("backend", ["simt", "auto"])
+def test_nhwc_conv2_weight_gradient(n, backend):
+    """conv2d_bwd_weight_nhwc (16 -> 32 channels, 14x14 -> 7x7): the tcgen05 split-K implicit GEMM (batch % 8 == 0,
+    backend != simt) and the CUDA-core kernel, dz in CHW and NHWC layout, twice in a row on one scratch buffer, with
+    and without accumulation, against autograd."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    lib = N.cuda()
+    F200.set_backend(backend)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    stream = torch.cuda.Stream()
+    st = C.c_void_p(stream.cuda_stream)
+    dz = torch.randn(n, 32, 7, 7, device="cuda")
+    a1 = torch.randn(n, 16, 14, 14, device="cuda")
+    dz_nhwc, a1_nhwc = dz.permute(0, 2, 3, 1).contiguous(), a1.permute(0, 2, 3, 1).contiguous()
+    w = torch.zeros(32, 16, 3, 3, device="cuda", requires_grad=True)
+    F.conv2d(a1, w, None, 2, 1).backward(dz)
+    want_w, want_b = w.grad, dz.sum((0, 2, 3))
+    shp = N.ConvShape(n, 16, 14, 14, 32, 7, 7, 3, 1, 2)
+    scratch = torch.zeros(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp)), dtype=torch.uint8, device="cuda")
+    tol = TOL["simt" if backend == "simt" else "tcgen05"]
+    torch.cuda.synchronize()
+    with torch.cuda.stream(stream):
+        for chw, src, acc in ((1, dz, 0), (0, dz_nhwc, 0), (1, dz, 1)):
+            dw = torch.full((32, 16, 3, 3), 7.0, device="cuda")
+            db = torch.full((32,), 7.0, device="cuda")
+            N.check(lib.b200cnn_conv2d_bwd_weight_nhwc(p(a1_nhwc), 0, p(src), chw, p(dw), p(db), acc, p(scratch), C.byref(shp), st), "bwd_weight")
+            stream.synchronize()
+            _close(dw, want_w + 7.0 * acc, tol)
+            _close(db, want_b + 7.0 * acc, tol)

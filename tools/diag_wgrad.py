@@ -33,3 +33,20 @@ for n in (256, 72, 8):
             if chw == 0:
                 for kx in range(3):
                     stat(f"   kx={kx}", dw[:, :, :, kx], wr.grad[:, :, :, kx])
+if os.environ.get("B200CNN_WG_DEBUG") == "1":
+    n = 256
+    dz = torch.randn(n, 32, 7, 7, device="cuda"); a1_nhwc = torch.randn(n, 14, 14, 16, device="cuda")
+    shp = N.ConvShape(n, 16, 14, 14, 32, 7, 7, 3, 1, 2)
+    scratch = torch.zeros(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp)), dtype=torch.uint8, device="cuda")
+    dw = torch.zeros(32, 16, 3, 3, device="cuda"); db = torch.zeros(32, device="cuda")
+    with torch.cuda.stream(stream):
+        for it in range(5):
+            lib.b200cnn_conv2d_bwd_weight_nhwc(p(a1_nhwc), 0, p(dz), 1, p(dw), p(db), 0, p(scratch), C.byref(shp), st)
+            torch.cuda.synchronize()
+    buf = (C.c_longlong * (12 * 16))()
+    lib.b200cnn_debug_wgrad_stamps.argtypes = [C.c_void_p, C.c_int]
+    print("stamps rc", lib.b200cnn_debug_wgrad_stamps(buf, 12 * 16))
+    names = ["entry", "pdl", "tma0", "b0", "mma0done", "tma1", "b1", "acc", "stored"]
+    for L in range(12):
+        row = [buf[L * 16 + i] for i in range(9)]
+        print(f"leader {L:2d}: " + " ".join(f"{names[i]}={(row[i] - row[0]) / 1.965e3:6.2f}" if row[i] else f"{names[i]}=   -- " for i in range(1, 9)))
