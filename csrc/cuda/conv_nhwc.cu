@@ -136,6 +136,12 @@ conv_bwd_weight_nhwc_kernel(const float* __restrict__ x, const float* __restrict
 // work on each item and are summed through shared memory.  Inner loop: one float4 of dz + one pixel -> 4 FMAs.
 constexpr int kC1Threads = 640;
 
+// Instrumentation (tools/diag_c1.py; off unless b200cnn_debug_c1_enable(1)): clock64 stamps of block 0 [0..7] and of
+// the block that ran the final reduction [8..15].
+__device__ long long g_c1_stamps[16];
+__device__ int g_c1_debug;
+#define C1_STAMP(slot) do { if (g_c1_debug && t == 0) g_c1_stamps[(slot)] = clock64(); } while (0)
+
 template <typename TIn>
 __global__ void __launch_bounds__(kC1Threads)
 conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restrict__ dz, float* __restrict__ partials,
@@ -152,8 +158,10 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
     float* xs = sm;                         // [ns][in_pad]
     float* gs = sm + size_t(spb) * in_pad;  // [ns][pix][OC]
     float* red = gs + size_t(spb) * out_sz; // [slices][nout]
+    if (blockIdx.x == 0) C1_STAMP(0);
     pdl_wait();
     pdl_launch_dependents();
+    if (blockIdx.x == 0) C1_STAMP(1);
     if (sizeof(TIn) == 1 && (in_sz & 3) == 0) {
         // four pixels per load
         const uchar4* x4 = reinterpret_cast<const uchar4*>(x + size_t(n0) * in_sz);
@@ -172,6 +180,7 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
         for (int i = t; i < ns * out_sz / 4; i += kC1Threads) reinterpret_cast<float4*>(gs)[i] = __ldg(gg + i);
     }
     __syncthreads();
+    if (blockIdx.x == 0) C1_STAMP(2);
     const int item = t % items, slice = t / items;
     if (slice < slices) {
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
@@ -218,6 +227,7 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
     // consistent __threadfence() in every thread: MEMBAR.SC.GPU x 640 threads was ~1 us of this kernel's tail.
     __shared__ unsigned is_last;
     __syncthreads();
+    if (blockIdx.x == 0) C1_STAMP(3);
     if (t == 0) {
         asm volatile("fence.acq_rel.gpu;" ::: "memory");
         const unsigned done = atomicInc(counter, gridDim.x - 1);  // wraps back to 0 for the next call
@@ -225,7 +235,9 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
         asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     __syncthreads();
+    if (blockIdx.x == 0) C1_STAMP(4);
     if (!is_last) return;
+    C1_STAMP(8);
     const int j = t % nout, part = t / nout, parts = kC1Threads / nout;
     if (part < parts) {
         // All of a thread's L2 loads in flight at once where possible (32, then 8, then 1): every batch is one
@@ -250,6 +262,7 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
         red[part * nout + j] = a;
     }
     __syncthreads();
+    C1_STAMP(9);
     if (t < nout) {
         float a = red[t];
         for (int sl = 1; sl < parts; sl++) a += red[sl * nout + t];
@@ -265,9 +278,17 @@ conv_bwd_weight_c1_nhwc_kernel(const TIn* __restrict__ x, const float* __restric
             *wdst -= *lr_dev * a;
         }
     }
+    C1_STAMP(10);
 }
 
 }  // namespace
+
+extern "C" int b200cnn_debug_c1_enable(int on) {
+    return cudaMemcpyToSymbol(g_c1_debug, &on, sizeof(int)) == cudaSuccess ? 0 : 1;
+}
+extern "C" int b200cnn_debug_c1_stamps(long long* out16) {
+    return cudaMemcpyFromSymbol(out16, g_c1_stamps, 16 * sizeof(long long)) == cudaSuccess ? 0 : 1;
+}
 
 int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks, int nw, int nb, int accumulate,
                          cudaStream_t st);
