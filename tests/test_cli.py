@@ -57,9 +57,10 @@ def test_cudampi_two_gpus(dataset_paths, repo_root):
     r = _run(PY + ["cudampi", "-np", "2", "--nepoch", "20", "--batch-size", "50", "--rate", "0.3"] + dataset_paths, repo_root)
     assert r.returncode == 0, r.stderr
     sums = re.findall(r"rank \d param_checksum=(\S+)", r.stderr)
-    assert len(sums) == 2 and sums[0] == sums[1]
-    assert re.search(r"^0 0 100$", r.stderr, re.M) and re.search(r"^1 100 200$", r.stderr, re.M)
-    assert int(re.search(r"ncorrect=(\d+)", r.stderr).group(1)) >= 45
+    tail = r.stderr[-3000:]  # shown when an assertion fails: which of the checks, and what the ranks printed
+    assert len(sums) == 2 and sums[0] == sums[1], tail
+    assert re.search(r"^0 0 100$", r.stderr, re.M) and re.search(r"^1 100 200$", r.stderr, re.M), r.stderr[:3000]
+    assert int(re.search(r"ncorrect=(\d+)", r.stderr).group(1)) >= 45, tail
 
 
 @pytest.mark.gpu
