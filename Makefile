@@ -23,7 +23,7 @@ LIBDIR := $(PKG)/lib
 BINDIR := bin
 OBJDIR := build
 
-CPU_SRCS := csrc/cpu/idx.cpp csrc/cpu/net.cpp csrc/cpu/comm.cpp csrc/cpu/trainer.cpp csrc/cpu/capi.cpp
+CPU_SRCS := csrc/cpu/idx.cpp csrc/cpu/net.cpp csrc/cpu/net_batch.cpp csrc/cpu/comm.cpp csrc/cpu/trainer.cpp csrc/cpu/capi.cpp
 CPU_OBJS := $(patsubst csrc/cpu/%.cpp,$(OBJDIR)/cpu/%.o,$(CPU_SRCS))
 
 CUDA_SRCS := $(wildcard csrc/cuda/*.cu) $(wildcard csrc/comm/*.cu)

@@ -54,6 +54,13 @@ void b200cnn_cpu_net_get_outputs(const b200cnn_cpu_net* n, double* y) { n->net.g
 void b200cnn_cpu_net_learn_outputs(b200cnn_cpu_net* n, const double* t) { n->net.learn_outputs(t); }
 double b200cnn_cpu_net_error_total(const b200cnn_cpu_net* n) { return n->net.error_total(); }
 void b200cnn_cpu_net_update(b200cnn_cpu_net* n, double rate) { n->net.update(rate); }
+int b200cnn_cpu_net_batch_supported(const b200cnn_cpu_net* n) { return n->net.batch_supported() ? 1 : 0; }
+void b200cnn_cpu_net_learn_batch(b200cnn_cpu_net* n, const double* xs, const double* targets, int count, double* sample_error) {
+    n->net.learn_batch(xs, targets, count, sample_error);
+}
+void b200cnn_cpu_net_forward_batch(b200cnn_cpu_net* n, const double* xs, int count, double* ys) {
+    n->net.forward_batch(xs, count, ys);
+}
 
 void b200cnn_cpu_net_get_params(const b200cnn_cpu_net* n, double* out) {
     std::vector<double> flat;

@@ -85,6 +85,17 @@ public:
 
     const Quirks& quirks() const { return quirks_; }
 
+    // ---- mini-batch fast path (net_batch.cpp) ------------------------------------------------------------
+    // learn_batch(xs, targets, n) is n calls of set_inputs + learn_outputs: gradients ACCUMULATE into
+    // u_weights / u_biases, sample_error[s] is what error_total() would have returned after sample s.  The
+    // difference is the schedule: the fully connected layers run as matrix-matrix loops over the whole batch, so
+    // their weights (2.5 MB for the first one: larger than L2) are streamed once per batch instead of three times
+    // per sample, which is what bounds the per-sample path.  Only the summation ORDER differs (results agree to
+    // rounding); convolutions run per sample as a row gather + register-blocked unit-stride loops.  Clean mode only.
+    bool batch_supported() const;
+    void learn_batch(const double* xs, const double* targets, int n, double* sample_error = nullptr);
+    void forward_batch(const double* xs, int n, double* ys);  // ys: [n][outputs of the last layer]
+
 private:
     void forward_full(size_t li);
     void backward_full(size_t li);
@@ -99,6 +110,25 @@ private:
     std::vector<Layer> layers_;
     Quirks quirks_;
     std::vector<double> scratch_;  // dLoss/d(pre-activation) of one output plane (backward_conv_fast)
+
+    struct BatchBuf {
+        std::vector<double> outputs, gradients, errors;  // [capacity][nnodes]
+        std::vector<int> argmax;                          // pool layers: [capacity][nnodes]
+        // convolution layers: weights / weight-gradient accumulators with rows padded to a multiple of 4, and the
+        // per-sample row-gather scratch (see net_batch.cpp)
+        std::vector<double> wpad, dwpad, rows, drows, dnet, img;
+        std::vector<int> gather, list;
+    };
+    std::vector<BatchBuf> batch_;  // one per layer
+    int batch_cap_ = 0;
+    void ensure_batch(int n);
+    void forward_layers_batch(const double* xs, int n);
+    void forward_full_batch(size_t li, int n);
+    void backward_full_batch(size_t li, int n);
+    void forward_conv_batch(size_t li, int n);
+    void backward_conv_batch(size_t li, int n);
+    void forward_pool_batch(size_t li, int n);
+    void backward_pool_batch(size_t li, int n);
 };
 
 }  // namespace b200cnn

@@ -24,6 +24,7 @@ void usage(const char* prog, bool dp) {
             "  --pool           conv(3x3,s1)+ReLU+maxpool(2x2) blocks instead of stride-2 convs\n"
             "  --ref-quirks     reproduce the reference's conv indexing / batching quirks\n"
             "  --save F / --load F   checkpoint the parameters\n"
+            "  --per-sample          clean mode: one sample at a time through the layers (default: mini-batch schedule)\n"
             "  --timing         report training images/s\n%s",
             prog, dp ? " per rank" : "", dp ? "  -np N            fork N ranks over shared memory\n" : "");
 }
@@ -66,6 +67,7 @@ int parse_options(int argc, char** argv, bool dp, TrainOptions& opt) {
         else if (a == "--save") { if (!(v = need("--save"))) return kUsage; opt.save_path = v; }
         else if (a == "--load") { if (!(v = need("--load"))) return kUsage; opt.load_path = v; }
         else if (a == "--ref-quirks") opt.ref_quirks = true;
+        else if (a == "--per-sample") opt.per_sample = true;
         else if (a == "--pool") opt.pool = true;
         else if (a == "--timing") opt.timing = true;
         else if (dp && (a == "-np" || a == "--np")) { if (!(v = need("-np"))) return kUsage; opt.np = atoi(v); }
@@ -127,6 +129,29 @@ int evaluate(Net& net, const IdxFile& images, const IdxFile& labels, bool log) {
     const int nclass = net.layer(net.num_layers() - 1).nnodes();
     std::vector<double> x(images.item_size()), y(nclass);
     int ncorrect = 0;
+    if (net.batch_supported()) {
+        // clean mode: 64 samples per pass over the fully connected weights
+        const int chunk = 64;
+        const size_t item = images.item_size();
+        std::vector<double> xs(size_t(chunk) * item), ys(size_t(chunk) * nclass);
+        for (int i0 = 0; i0 < ntests; i0 += chunk) {
+            const int nb = std::min(chunk, ntests - i0);
+            for (int b = 0; b < nb; b++) {
+                const uint8_t* img = images.get3(i0 + b);
+                for (size_t j = 0; j < item; j++) xs[b * item + j] = img[j] / 255.0;
+            }
+            net.forward_batch(xs.data(), nb, ys.data());
+            for (int b = 0; b < nb; b++) {
+                const double* yb = &ys[size_t(b) * nclass];
+                int mj = -1;
+                for (int j = 0; j < nclass; j++)
+                    if (mj < 0 || yb[mj] < yb[j]) mj = j;
+                if (mj == labels.get1(i0 + b)) ncorrect++;
+                if (log && ((i0 + b) % 1000) == 0) fprintf(stderr, "i=%d\n", i0 + b);
+            }
+        }
+        return ncorrect;
+    }
     for (int i = 0; i < ntests; i++) {
         const uint8_t* img = images.get3(i);
         for (size_t j = 0; j < x.size(); j++) x[j] = img[j] / 255.0;
@@ -160,7 +185,33 @@ int run_serial(const TrainOptions& opt) {
     double etotal = 0;
     int pending = 0, since_log = 0;
     const double t0 = now_s();
-    for (long i = 0; i < total; i++) {
+    const bool batched = !opt.ref_quirks && !opt.per_sample && net.batch_supported();
+    if (batched) {
+        // Same samples, same order, same updates as the loop below; the mini-batch goes through Net::learn_batch.
+        const int B = opt.batch_size;
+        const size_t item = data.train_x.item_size();
+        std::vector<double> xs(size_t(B) * item), ys(size_t(B) * nclass), errs(B);
+        for (long i = 0; i < total;) {
+            const int nb = int(std::min<long>(B, total - i));
+            for (int b = 0; b < nb; b++) {
+                const int index = rng.next() % train_size;
+                load_sample(data.train_x, data.train_y, index, &xs[b * item], &ys[size_t(b) * nclass], nclass);
+            }
+            net.learn_batch(xs.data(), ys.data(), nb, errs.data());
+            for (int b = 0; b < nb; b++) {
+                etotal += errs[b];
+                since_log++;
+                if (((i + b) % opt.log_every) == 0) {
+                    fprintf(stderr, "i=%ld, error=%.4f\n", i + b, etotal / since_log);
+                    etotal = 0;
+                    since_log = 0;
+                }
+            }
+            net.update(opt.rate / nb);
+            i += nb;
+        }
+    }
+    for (long i = 0; !batched && i < total; i++) {
         // Sampling with replacement from the same stream that initialised the weights (cnn.c:455).
         const int index = rng.next() % train_size;
         load_sample(data.train_x, data.train_y, index, x.data(), y.data(), nclass);
@@ -241,6 +292,32 @@ int run_data_parallel(const TrainOptions& opt, Comm& comm) {
     for (int epoch = 0; epoch < opt.nepoch; epoch++) {
         if (rank == 0) fprintf(stderr, "epoch = %d\n", epoch);
         int pending = 0;
+        if (!opt.per_sample && net.batch_supported()) {
+            const int B = opt.batch_size;
+            const size_t item = data.train_x.item_size();
+            std::vector<double> xs(size_t(B) * item), ys(size_t(B) * nclass), errs(B);
+            for (int idx = start; idx < end;) {
+                const int nb = std::min(B, end - idx);
+                for (int b = 0; b < nb; b++)
+                    load_sample(data.train_x, data.train_y, idx + b, &xs[b * item], &ys[size_t(b) * nclass], nclass);
+                net.learn_batch(xs.data(), ys.data(), nb, errs.data());
+                net.gather_updates(flat);
+                comm.allreduce_sum(flat.data(), flat.size());
+                net.scatter_updates(flat);
+                net.update(opt.rate / (double(nb) * ws));
+                for (int b = 0; b < nb; b++) {
+                    etotal += errs[b];
+                    since_log++;
+                    if (rank == 0 && ((idx + b - start) % opt.log_every) == 0) {
+                        fprintf(stderr, "    idx = %d, error = %f\n", idx + b, etotal / since_log);
+                        etotal = 0;
+                        since_log = 0;
+                    }
+                }
+                idx += nb;
+            }
+            continue;
+        }
         for (int idx = start; idx < end; idx++) {
             load_sample(data.train_x, data.train_y, idx, x.data(), y.data(), nclass);
             net.set_inputs(x.data());

@@ -25,7 +25,8 @@ struct TrainOptions {
     int log_every = 1000;    // cnn.c:470
     int synthetic = 0;       // >0: generate this many training samples instead of reading files
     int synthetic_test = 0;  // test samples for --synthetic (default: synthetic/5, at least 100)
-    bool ref_quirks = false; // reproduce D1/D2/D4 for diffing against the unmodified cnn.c
+    bool ref_quirks = false;  // reproduce D1/D2/D4 for diffing against the unmodified cnn.c
+    bool per_sample = false;  // clean mode: keep the one-sample-at-a-time schedule (A/B against Net::learn_batch)
     bool pool = false;       // conv -> relu -> 2x2 max-pool variant of the topology
     std::string save_path, load_path;
     int np = 0;              // cnnmpi only: ranks to fork (0 = take RANK/WORLD_SIZE from the env)

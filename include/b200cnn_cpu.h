@@ -43,6 +43,13 @@ void b200cnn_cpu_net_set_inputs(b200cnn_cpu_net* net, const double* x);
 void b200cnn_cpu_net_get_outputs(const b200cnn_cpu_net* net, double* y);
 void b200cnn_cpu_net_learn_outputs(b200cnn_cpu_net* net, const double* target);
 double b200cnn_cpu_net_error_total(const b200cnn_cpu_net* net);
+/* Mini-batch schedule (no counterpart in the reference, which only has the per-sample calls above): the same
+ * accumulation into the update buffers as n x (set_inputs + learn_outputs), with the fully connected layers run
+ * as matrix-matrix loops and the convolutions as row gathers; sample_error[n] (may be NULL) receives what
+ * error_total() would have returned after each sample.  Falls back to the per-sample calls in quirks mode. */
+int b200cnn_cpu_net_batch_supported(const b200cnn_cpu_net* net);
+void b200cnn_cpu_net_learn_batch(b200cnn_cpu_net* net, const double* xs, const double* targets, int n, double* sample_error);
+void b200cnn_cpu_net_forward_batch(b200cnn_cpu_net* net, const double* xs, int n, double* ys);
 void b200cnn_cpu_net_update(b200cnn_cpu_net* net, double rate);
 
 /* Flat views, layer order, weights then biases per layer. */

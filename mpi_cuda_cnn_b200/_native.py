@@ -81,6 +81,9 @@ def cpu():
     _sig(lib, "b200cnn_cpu_net_get_outputs", None, vp, c_double_p)
     _sig(lib, "b200cnn_cpu_net_learn_outputs", None, vp, c_double_p)
     _sig(lib, "b200cnn_cpu_net_error_total", d, vp)
+    _sig(lib, "b200cnn_cpu_net_batch_supported", i, vp)
+    _sig(lib, "b200cnn_cpu_net_learn_batch", None, vp, c_double_p, c_double_p, i, c_double_p)
+    _sig(lib, "b200cnn_cpu_net_forward_batch", None, vp, c_double_p, i, c_double_p)
     _sig(lib, "b200cnn_cpu_net_update", None, vp, d)
     _sig(lib, "b200cnn_cpu_net_get_params", None, vp, c_double_p)
     _sig(lib, "b200cnn_cpu_net_set_params", None, vp, c_double_p)

@@ -102,6 +102,30 @@ class CpuNet:
     def error_total(self):
         return self.lib.b200cnn_cpu_net_error_total(self.handle)
 
+    # mini-batch schedule (csrc/cpu/net_batch.cpp) ------------------------------------------------
+    @property
+    def batch_supported(self):
+        return bool(self.lib.b200cnn_cpu_net_batch_supported(self.handle))
+
+    def learn_batch(self, xs, targets):
+        """n x (set_inputs + learn_outputs) in one call; returns the per-sample error_total() values."""
+        xs = np.ascontiguousarray(xs, dtype=np.float64)
+        n = xs.shape[0]
+        xs = xs.reshape(n, -1)
+        t = np.ascontiguousarray(targets, dtype=np.float64).reshape(n, -1)
+        err = np.empty(n, dtype=np.float64)
+        self.lib.b200cnn_cpu_net_learn_batch(self.handle, _dp(xs), _dp(t), n, _dp(err))
+        return err
+
+    def forward_batch(self, xs):
+        xs = np.ascontiguousarray(xs, dtype=np.float64)
+        n = xs.shape[0]
+        xs = xs.reshape(n, -1)
+        info = self.layer_info(self.num_layers - 1)
+        ys = np.empty((n, info["depth"] * info["width"] * info["height"]), dtype=np.float64)
+        self.lib.b200cnn_cpu_net_forward_batch(self.handle, _dp(xs), n, _dp(ys))
+        return ys
+
     def update(self, rate):
         self.lib.b200cnn_cpu_net_update(self.handle, rate)
 

@@ -79,6 +79,55 @@ def test_forward_backward_vs_torch_fp64(pool):
     assert np.all(net.get_updates() == 0)
 
 
+@pytest.mark.parametrize("pool", [False, True])
+@pytest.mark.parametrize("n", [1, 7, 32])
+def test_learn_batch_equals_per_sample_calls_and_torch(pool, n):
+    """The mini-batch schedule (net_batch.cpp) against the per-sample Layer_* calls and against autograd: gradients,
+    per-sample metric, outputs; over several batches with an update in between (stale scratch state shows up on the
+    second batch, not the first)."""
+    from mpi_cuda_cnn_b200.engine import mnist_layers, pool_layers
+
+    layers = pool_layers() if pool else mnist_layers()
+    a, b = CpuNet.from_layers(layers, seed=3), CpuNet.from_layers(layers, seed=3)
+    assert b.batch_supported
+    for it in range(3):
+        x, y = make_synthetic(n, seed=11 + it)
+        xs = x.astype(np.float64) / 255.0
+        onehot = np.eye(10)[y]
+        errs_a = []
+        for i in range(n):
+            a.set_inputs(xs[i])
+            a.learn_outputs(onehot[i])
+            errs_a.append(a.error_total())
+        errs_b = b.learn_batch(xs, onehot)
+        assert np.allclose(errs_b, errs_a, rtol=1e-12, atol=1e-15)
+        ua, ub = a.get_updates(), b.get_updates()
+        assert np.allclose(ub, ua, rtol=1e-10, atol=1e-12 * max(1.0, np.abs(ua).max()))
+        if it == 0:
+            model = load_dense_params(RefCNN(pool=pool), b.get_params())
+            model.loss_sum(torch.from_numpy(xs)[:, None], torch.from_numpy(y.astype(np.int64))).backward()
+            assert np.allclose(ub, dense_grads(model), atol=1e-10)
+        assert np.allclose(b.get_outputs(), a.get_outputs(), atol=1e-13)  # single-sample view = the last sample
+        assert np.allclose(b.forward_batch(xs)[-1], a.get_outputs(), atol=1e-13)
+        a.update(0.1 / n)
+        b.update(0.1 / n)
+        assert np.allclose(b.get_params(), a.get_params(), rtol=1e-10, atol=1e-12)
+
+
+def test_learn_batch_falls_back_in_quirks_mode():
+    from mpi_cuda_cnn_b200.engine import mnist_layers
+
+    a, b = CpuNet.from_layers(mnist_layers(), seed=1, quirks=7), CpuNet.from_layers(mnist_layers(), seed=1, quirks=7)
+    assert not b.batch_supported
+    x, y = make_synthetic(3, seed=2)
+    xs, onehot = x.astype(np.float64) / 255.0, np.eye(10)[y]
+    for i in range(3):
+        a.set_inputs(xs[i])
+        a.learn_outputs(onehot[i])
+    b.learn_batch(xs, onehot)
+    assert np.array_equal(a.get_updates(), b.get_updates())  # same code path, bit for bit
+
+
 def test_quirk_d1_shared_conv_slice():
     clean, quirky = CpuNet.mnist(seed=0), CpuNet.mnist(seed=0, quirks=QUIRKS_REFERENCE)
     x, y = make_synthetic(1, seed=9)
