@@ -218,7 +218,9 @@ int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, bool last, cudaSt
 // branches of the CUDA graph.)  Order on the side stream per layer:
 //     wait(dz ready) -> dW/db kernel(s) -> wait(this layer's data gradient issued) -> fused update hook
 // The hook must come after the data-gradient kernel because a two-shot / NVLS update may overwrite the
-// layer's weights on this GPU from a peer.
+// layer's weights on this GPU from a peer.  The step's LAST bucket is the exception: it is launched on `st`
+// itself after the side stream has been joined (second flag channel of the communicator), because it is the tail
+// of the step and every stream hop in front of it is exposed latency.
 int enqueue_sgd_range(b200cnn_engine* e, size_t begin, size_t end, cudaStream_t st, int* launches);
 
 int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch, cudaStream_t st, int* launches,

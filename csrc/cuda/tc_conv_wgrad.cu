@@ -53,7 +53,7 @@ struct WgradArgs {
     float* dw;             // OIHW [32][16][3][3]
     float* db;             // [32]
     int n;
-    long long* dbg;        // instrumentation (B200CNN_WG_DEBUG=1): clock64 stamps of the cluster leaders, [ky*4+z][16] for z < 4
+    long long* dbg;        // instrumentation (B200CNN_WG_DEBUG=1): clock64 stamps of CTAs (ky, z < 4), [ky*4+z][16]
 };
 
 #define WG_STAMP(i) do { if (a.dbg && blockIdx.z < 4) a.dbg[(ky * 4 + blockIdx.z) * 16 + (i)] = clock64(); } while (0)
@@ -249,7 +249,7 @@ wgrad_reduce_kernel(const float* __restrict__ part, int splits, float* __restric
 }  // namespace
 
 static long long* g_wg_dbg = nullptr;
-// Instrumentation read-back (tools/diag_wgrad.py): 16 clock64 stamps per cluster leader of the last launch.
+// Instrumentation read-back (tools/diag_wgrad.py): 16 clock64 stamps per instrumented CTA of the last launch.
 extern "C" int b200cnn_debug_wgrad_stamps(long long* out, int count) {
     if (!g_wg_dbg || count > 64 * 16) return 1;
     return cudaMemcpy(out, g_wg_dbg, size_t(count) * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 2;
