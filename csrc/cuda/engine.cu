@@ -273,7 +273,8 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             else
                 rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0,
                                               li == 1 ? e->scratch1 : e->scratch, &s, ws);
-            if (launches) (*launches) += 2;
+            // (the single-channel kernel reduces in its last block: one launch; every other path is kernel + reduce)
+            if (launches) (*launches) += (fast && li <= 2 && p.d.depth == 1) ? 1 : 2;
         }
         if (rc) return rc;
 
