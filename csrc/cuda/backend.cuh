@@ -54,6 +54,13 @@ size_t tc_conv3x3s2_bwd_weight_scratch_floats(int n);
 int tc_conv3x3s2_bwd_weight(const float* x_nhwc, const float* dz, int dz_is_chw, float* dw, float* db, int accumulate,
                             float* part, const b200cnn_conv_shape* s, cudaStream_t st);
 
+// tc_conv1_wgrad.cu: weight gradient of the 1 -> 16 channel first convolution on the tensor cores (opt-in, see the file)
+bool tc_conv1_bwd_weight_enabled();
+bool tc_conv1_bwd_weight_supported(const b200cnn_conv_shape* s, int max_partials);
+int tc_conv1_bwd_weight(const uint8_t* x, const float* dz_nhwc, float* dw, float* db, int accumulate, float* partials,
+                        unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st, float* sgd_w, float* sgd_b,
+                        const float* lr_dev);
+
 // conv_nhwc.cu / conv.cu
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
 int nhwc_bwd_weight_chunks(int n, int* spb_out);

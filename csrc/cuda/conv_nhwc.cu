@@ -340,6 +340,9 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         if (items > kC1Threads || nout > kC1Threads) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: layer too large for the single-channel kernel");
         const int slices = kC1Threads / items;
         unsigned* counter = counter_in ? counter_in : header;
+        if (x_is_u8 && tc_conv1_bwd_weight_enabled() && tc_conv1_bwd_weight_supported(s, chunks))
+            return tc_conv1_bwd_weight(static_cast<const uint8_t*>(x), dz, dw, db, accumulate, partials, counter, s, st, sgd_w, sgd_b,
+                                       lr_dev);
         const size_t smem = (size_t(spb) * (((s->h * s->w + 3) & ~3) + size_t(s->oh) * s->ow * s->oc) + size_t(std::max(slices, kC1Threads / nout)) * nout) * sizeof(float);
         if (smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: samples do not fit shared memory");
         if (x_is_u8) {
