@@ -524,6 +524,19 @@ int comm_join(b200cnn_comm* c, cudaStream_t st) {
     return 0;
 }
 
+// The last flag slot is reserved for exchanges done inside other kernels (phase 0 only, one-shot, no exit barrier:
+// gradients are double-buffered by step parity).
+void comm_tail_xchg(const b200cnn_comm* c, TailXchg* out) {
+    out->world = c->view.world;
+    out->rank = c->view.rank;
+    out->slot = kMaxBlocks - 1;
+    for (int r = 0; r < kMaxRanks; r++) out->region[r] = c->view.region[r];
+    out->params_off = c->view.params_off;
+    out->grads_off = c->view.grads_off[c->parity];
+    out->seq = c->view.seq + out->slot;
+    out->errflag = c->view.errflag;
+}
+
 float* comm_current_grads(b200cnn_comm* c) { return b200cnn_comm_grads(c, c->parity); }
 void comm_flip_parity(b200cnn_comm* c) { c->parity ^= 1; }
 int comm_parity(const b200cnn_comm* c) { return c->parity; }

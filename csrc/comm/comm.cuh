@@ -5,9 +5,23 @@
 #include <cstddef>
 #include <cstdint>
 
+#include "b200cnn_comm.h"
+
 struct b200cnn_comm;
 
 namespace b200cnn {
+
+// What a kernel OUTSIDE the communicator needs to exchange a small slice with its peers itself (the weight-gradient
+// kernel of the first convolution does its own one-shot all-reduce + SGD in the block that finishes last:
+// csrc/cuda/tc_conv1_wgrad.cu, csrc/comm/xchg_device.cuh).  Filled by comm_tail_xchg() for the step being enqueued.
+struct TailXchg {
+    int world = 1, rank = 0, slot = 0;
+    char* region[B200CNN_COMM_MAX_RANKS] = {};
+    size_t params_off = 0, grads_off = 0;  // byte offsets inside a region; grads: the half this step writes
+    uint32_t* seq = nullptr;               // this rank's sequence counter of flag slot `slot`
+    uint32_t* errflag = nullptr;           // raised instead of hanging when a peer does not show up
+};
+void comm_tail_xchg(const b200cnn_comm* c, TailXchg* out);
 
 // Enqueue the fused all-reduce + 1/world + SGD for floats [offset, offset + count) of the flat
 // parameter / gradient buffers.  The kernel runs on the communicator's own stream, ordered after

@@ -57,16 +57,18 @@ int tc_conv3x3s2_bwd_weight(const float* x_nhwc, const float* dz, int dz_is_chw,
 // tc_conv1_wgrad.cu: weight gradient of the 1 -> 16 channel first convolution on the tensor cores (opt-in, see the file)
 bool tc_conv1_bwd_weight_enabled();
 bool tc_conv1_bwd_weight_supported(const b200cnn_conv_shape* s, int max_partials);
+struct TailXchg;  // csrc/comm/comm.cuh
 int tc_conv1_bwd_weight(const uint8_t* x, const float* dz_nhwc, float* dw, float* db, int accumulate, float* partials,
                         unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st, float* sgd_w, float* sgd_b,
-                        const float* lr_dev);
+                        const float* lr_dev, const TailXchg* xchg = nullptr, long w_off = 0, long b_off = 0);
 
 // conv_nhwc.cu / conv.cu
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
 int nhwc_bwd_weight_chunks(int n, int* spb_out);
 int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
                          float* partials, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st,
-                         float* sgd_w = nullptr, float* sgd_b = nullptr, const float* lr_dev = nullptr);
+                         float* sgd_w = nullptr, float* sgd_b = nullptr, const float* lr_dev = nullptr,
+                         const TailXchg* xchg = nullptr, long w_off = 0, long b_off = 0);
 int simt_conv2d_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* y, const b200cnn_conv_shape* s,
                     int act, int nhwc_out, cudaStream_t st);
 int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks, int nw, int nb, int accumulate,

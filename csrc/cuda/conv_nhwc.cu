@@ -322,7 +322,9 @@ static bool tc_wgrad_enabled() {
 // itself); NULL = the word right after this layer's partials.
 int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
                          float* partials, unsigned* counter_in, const b200cnn_conv_shape* s, cudaStream_t st, float* sgd_w,
-                         float* sgd_b, const float* lr_dev) {
+                         float* sgd_b, const float* lr_dev, const TailXchg* xchg, long w_off, long b_off) {
+    if (xchg && !(s->c == 1 && x_is_u8 && tc_conv1_bwd_weight_enabled()))
+        return set_error(kInvalidValue, "nhwc_conv_bwd_weight: the in-kernel all-reduce exists only in the tensor-core conv1 kernel");
     if (sgd_w && s->c != 1) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: the fused update exists only in the single-channel kernel");
     if (!nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: unsupported shape");
     // Scratch layout: [128-byte header | partial sums].  The header's first word is the completion counter of the
@@ -342,7 +344,8 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
         unsigned* counter = counter_in ? counter_in : header;
         if (x_is_u8 && tc_conv1_bwd_weight_enabled() && tc_conv1_bwd_weight_supported(s, chunks))
             return tc_conv1_bwd_weight(static_cast<const uint8_t*>(x), dz, dw, db, accumulate, partials, counter, s, st, sgd_w, sgd_b,
-                                       lr_dev);
+                                       lr_dev, xchg, w_off, b_off);
+        if (xchg) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: shape not supported by the tensor-core conv1 kernel");
         const size_t smem = (size_t(spb) * (((s->h * s->w + 3) & ~3) + size_t(s->oh) * s->ow * s->oc) + size_t(std::max(slices, kC1Threads / nout)) * nout) * sizeof(float);
         if (smem > 200 * 1024) return set_error(kInvalidValue, "nhwc_conv_bwd_weight: samples do not fit shared memory");
         if (x_is_u8) {

@@ -223,6 +223,14 @@ int layer_grads_ready(b200cnn_engine* e, const EngineLayer& l, bool last, cudaSt
 // of the step and every stream hop in front of it is exposed latency.
 int enqueue_sgd_range(b200cnn_engine* e, size_t begin, size_t end, cudaStream_t st, int* launches);
 
+static bool fused_tail_requested() {
+    static const bool on = [] {
+        const char* v = getenv("B200CNN_FUSED_TAIL");
+        return v && v[0] == '1';
+    }();
+    return on;
+}
+
 int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch, cudaStream_t st, int* launches,
                      bool head_done = false, bool fuse_update = false) {
     auto& L = e->layers;
@@ -231,6 +239,20 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
     cudaStream_t side = e->side;
     e->bucket_lo = e->bucket_hi = -1;
     e->tail_lo = e->tail_hi = -1;
+    // Opt-in (B200CNN_FUSED_TAIL=1 with B200CNN_TC_C1=1, not validated on several GPUs yet — NOTES_NEXT.md): the first
+    // convolution's weight-gradient kernel all-reduces its 160 numbers itself in its last block and the second
+    // convolution's slice goes out on the side stream as soon as it exists, so no collective kernel is left on the
+    // main stream after the last kernel of backward.
+    TailXchg xchg;
+    bool fused_tail = false;
+    if (e->comm && fast && fused_tail_requested() && tc_conv1_bwd_weight_enabled() && is_u8 && L.size() > 3 &&
+        L[1].d.type == B200CNN_LAYER_CONV && L[0].d.depth == 1 && L[2].d.type == B200CNN_LAYER_CONV) {
+        const b200cnn_conv_shape s1 = conv_shape(L[0], L[1], batch);
+        if (tc_conv1_bwd_weight_supported(&s1, nhwc_bwd_weight_chunks(batch, nullptr))) {
+            comm_tail_xchg(e->comm, &xchg);
+            fused_tail = xchg.world > 1;
+        }
+    }
     for (size_t li = L.size() - 1; li >= 1; li--) {
         EngineLayer& l = L[li];
         EngineLayer& p = L[li - 1];
@@ -266,9 +288,11 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             const b200cnn_conv_shape s = conv_shape(p, l, batch);
             if (fast && li <= 2) {
                 const bool fuse = fuse_update && li == 1;  // single GPU: this kernel's last block also applies the update
+                const bool xc = fused_tail && li == 1;  // this kernel exchanges its result with the peers itself
                 rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/li == 2, grads + l.w_off, grads + l.b_off, 0,
                                           li == 1 ? e->scratch1 : e->scratch, reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, ws,
-                                          fuse ? e->params + l.w_off : nullptr, fuse ? e->params + l.b_off : nullptr, e->lr_dev);
+                                          fuse ? e->params + l.w_off : nullptr, fuse ? e->params + l.b_off : nullptr, e->lr_dev,
+                                          xc ? &xchg : nullptr, long(l.w_off), long(l.b_off));
             }
             else
                 rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0,
@@ -307,7 +331,21 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
                 B200CNN_CUDA(cudaEventRecord(e->ev_data, st));
                 B200CNN_CUDA(cudaStreamWaitEvent(side, e->ev_data, 0));
             }
-            if ((rc = layer_grads_ready(e, l, last, side, launches))) return rc;
+            if (fused_tail && li == 2) {
+                // (anything the layers above left in the bucket goes first, in order, on the communicator's stream)
+                if (e->bucket_lo >= 0) {
+                    if ((rc = comm_allreduce_sgd_slice(e->comm, size_t(e->bucket_lo), size_t(e->bucket_hi - e->bucket_lo), e->lr_dev, side))) return rc;
+                    e->bucket_lo = e->bucket_hi = -1;
+                    if (launches) (*launches)++;
+                }
+                const long end = l.b_off + long(round_up(size_t(l.nb), kAlignFloats));
+                if ((rc = comm_allreduce_sgd_inline(e->comm, size_t(l.w_off), size_t(end - l.w_off), e->lr_dev, side))) return rc;
+                if (launches) (*launches)++;
+            } else if (fused_tail && li == 1) {
+                // exchanged inside its weight-gradient kernel
+            } else if ((rc = layer_grads_ready(e, l, last, side, launches))) {
+                return rc;
+            }
         }
     }
     // Join: everything on the side stream is ordered before whatever follows on `st`.

@@ -20,6 +20,7 @@
 // Replaces the weight half of Layer_feedBack_conv (/root/reference/cnn.c:236,242) for the first convolution.
 #include <cstdlib>
 
+#include "../comm/xchg_device.cuh"
 #include "backend.cuh"
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -52,6 +53,12 @@ struct C1Args {
     float* sgd_b;
     const float* lr_dev;
     int n, accumulate;
+    // Data parallel (xc.world > 1): the block that finishes last also all-reduces these 160 numbers with the peers and
+    // applies the averaged SGD step to this rank's replica (one-shot: every rank adds all ranks' values in rank
+    // order, so replicas stay bitwise identical).  dw / db then point into this rank's peer-visible gradient buffer,
+    // w_off / b_off are their float offsets inside it (and of the parameters inside the parameter buffer).
+    TailXchg xc;
+    long w_off, b_off;
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -193,6 +200,19 @@ tc_conv1_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_dz, C1Args a
             *wdst -= *a.lr_dev * acc;
         }
     }
+    if (a.xc.world > 1) {
+        // compute + collective in one kernel: conv1's gradient never waits for a separate all-reduce launch
+        const uint32_t seq = xchg::all_ranks_ready(a.xc);
+        if (t < kNOut) {
+            const size_t idx = size_t(t < kNW ? a.w_off + t : a.b_off + (t - kNW));
+            float s = 0.f;
+            for (int k = 0; k < a.xc.world; k++)
+                s += xchg::ld_peer(reinterpret_cast<const float*>(a.xc.region[k] + a.xc.grads_off) + idx);
+            float* w = reinterpret_cast<float*>(a.xc.region[a.xc.rank] + a.xc.params_off) + idx;
+            *w -= (*a.lr_dev / float(a.xc.world)) * s;
+        }
+        if (t == 0) *a.xc.seq = seq;
+    }
 }
 
 }  // namespace
@@ -213,13 +233,15 @@ bool tc_conv1_bwd_weight_supported(const b200cnn_conv_shape* s, int max_partials
 // x: uint8 [n][28][28]; dz: NHWC [n][14][14][16]; partials: ceil(n/2) * 160 floats; counter: one zero word.
 int tc_conv1_bwd_weight(const uint8_t* x, const float* dz_nhwc, float* dw, float* db, int accumulate, float* partials,
                         unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st, float* sgd_w, float* sgd_b,
-                        const float* lr_dev) {
+                        const float* lr_dev, const TailXchg* xchg, long w_off, long b_off) {
+    if (xchg && xchg->world > 1 && (accumulate || sgd_w || !lr_dev || !dw || !db))
+        return set_error(kInvalidValue, "tc_conv1_bwd_weight: the in-kernel all-reduce needs dw/db in the gradient buffer, no accumulation, no local update");
     CUtensorMap tm;
     const uint64_t dims[2] = {32, uint64_t(s->n) * kPairs};
     const uint64_t strides[2] = {0, 128};
     const uint32_t box[2] = {32, uint32_t(kRows)};
     if (int rc = encode_tmap_f32(&tm, dz_nhwc, 2, dims, strides, box, nullptr, kTmaSw128Atom32)) return rc;
-    C1Args a{x, partials, dw, db, counter, sgd_w, sgd_b, lr_dev, s->n, accumulate};
+    C1Args a{x, partials, dw, db, counter, sgd_w, sgd_b, lr_dev, s->n, accumulate, xchg ? *xchg : TailXchg{}, w_off, b_off};
     static bool configured = false;
     if (!configured) {
         B200CNN_CUDA(cudaFuncSetAttribute(tc_conv1_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmem)));
