@@ -20,6 +20,7 @@
 #include "../cuda/common.cuh"
 #include "b200cnn_comm.h"
 #include "comm.cuh"
+#include "ll.cuh"
 
 namespace b200cnn {
 
@@ -37,7 +38,15 @@ struct CommView {
     size_t params_off, grads_off[2];
     uint32_t* seq;     // local sequence counters [emulate ? world : 1][kMaxBlocks]
     uint32_t* errflag; // local
+    size_t ll_off;     // byte offset of the push-protocol inboxes inside a region (ll.cuh)
+    ll::Counters* ll_ctr;  // local [emulate ? world : 1][ll::kChannels]
 };
+
+constexpr int kLLMaxBlocks = 64;
+// "Weights have landed" flags of the two-shot push algorithm: [channel 0..1][source rank][block] words in the second
+// half of the flag block.
+constexpr size_t kWFlagOffset = 8192;
+static_assert(kWFlagOffset + 2 * kMaxRanks * kLLMaxBlocks * sizeof(uint32_t) <= B200CNN_COMM_FLAG_BYTES, "flag block too small");
 
 enum Op { kOpSgd = 0, kOpReduceOnly = 1, kOpBroadcast = 2, kOpBarrier = 3 };
 
@@ -84,8 +93,11 @@ __device__ __forceinline__ uint32_t* flag_ptr(char* region, int block, int phase
 
 // Cross-rank barrier between the blocks with this blockIdx.x on every rank.  All earlier global
 // writes of the CTA are published (CTA barrier, then a cumulative release at system scope).
-__device__ void signal_and_wait(const CommView& v, int rank, int phase, uint32_t seq, int slot) {
+// Returns true if a peer never showed up (~2 s): the caller must then skip its update and stores — reducing
+// incomplete data would silently corrupt the replicas; the error flag is what the host polls.
+__device__ bool signal_and_wait(const CommView& v, int rank, int phase, uint32_t seq, int slot) {
     __syncthreads();
+    int timed_out = 0;
     if (threadIdx.x < v.world && int(threadIdx.x) != rank) {
         const int peer = threadIdx.x;
         st_release_sys(flag_ptr(v.region[peer], slot, phase, rank), seq);
@@ -96,11 +108,12 @@ __device__ void signal_and_wait(const CommView& v, int rank, int phase, uint32_t
         while (int32_t(ld_acquire_sys(mine) - seq) < 0) {
             if (clock64() - t0 > kSpinTimeoutCycles) {
                 atomicExch(v.errflag, 1u);
+                timed_out = 1;
                 break;
             }
         }
     }
-    __syncthreads();
+    return __syncthreads_or(timed_out) != 0;
 }
 
 __device__ __forceinline__ float4 add4(float4 a, const float4& b) {
@@ -178,7 +191,7 @@ allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ l
     uint32_t* seq_slot = v.seq + (v.emulate ? rank : 0) * kMaxBlocks + slot;
     const uint32_t seq = *seq_slot + 1;
 
-    signal_and_wait(v, rank, 0, seq, slot);  // every rank's inputs for this call are complete
+    if (signal_and_wait(v, rank, 0, seq, slot)) return;  // every rank's inputs for this call are complete (or: give up)
 
     const float4* g[kMaxRanks];
 #pragma unroll
@@ -225,7 +238,7 @@ allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ l
             float4 keep[4];
             int nkeep = 0;
             for (size_t i = tid; i < n4 && nkeep < 4; i += nthreads) keep[nkeep++] = reduce_ranks<W>(g, world, i);
-            signal_and_wait(v, rank, 1, seq, slot);
+            if (signal_and_wait(v, rank, 1, seq, slot)) return;
             nkeep = 0;
             for (size_t i = tid; i < n4 && nkeep < 4; i += nthreads) g_local[i] = keep[nkeep++];
         }
@@ -284,6 +297,149 @@ allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ l
     if (threadIdx.x == 0) *seq_slot = seq;
 }
 
+// ---- push protocol (ll.cuh): one-hop all-reduce + SGD -------------------------------------------------------------
+__device__ __forceinline__ uint32_t* wflag_ptr(char* region, int ch, int src, int block) {
+    return reinterpret_cast<uint32_t*>(region + kWFlagOffset) + (ch * kMaxRanks + src) * kLLMaxBlocks + block;
+}
+
+__device__ __forceinline__ ll::Channel make_channel(const CommView& v, int rank, int ch) {
+    ll::Channel c;
+    c.world = v.world;
+    c.rank = rank;
+    c.ch = ch;
+#pragma unroll
+    for (int k = 0; k < kMaxRanks; k++) c.region[k] = v.region[k];
+    c.inbox_off = v.ll_off;
+    c.ctr = v.ll_ctr + (v.emulate ? rank : 0) * ll::kChannels + ch;
+    c.errflag = v.errflag;
+    return c;
+}
+
+// one-shot (two_shot == 0): every rank pushes its whole slice into every peer's inbox, then adds what arrived in its
+//   own inbox to its own gradient in rank order and updates its own weights.  One one-way NVLink trip, no barrier.
+// two-shot: rank r owns shard r.  Every rank pushes shard s of its gradient to rank s (reduce-scatter, one trip);
+//   the owner adds in rank order, computes the UPDATED WEIGHTS and stores them into every rank's parameter buffer
+//   (second trip), then raises one flag per block in every peer.  Nobody waits for those flags here: the consumer of
+//   the weights does, one step later (ll_wait_weights_kernel), so the second trip is off the critical path.
+template <int W>
+__global__ void __launch_bounds__(kCommThreads)
+ll_allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict__ lr_dev, float lr_imm, int two_shot,
+                    int parity, int op, int ch) {
+    const int rank = v.emulate ? int(blockIdx.y) : v.rank;
+    const int world = W > 0 ? W : v.world;
+    const ll::Channel c = make_channel(v, rank, ch);
+    const uint32_t tag = c.ctr->calls + 1;  // bumped by the block that finishes last, i.e. after every block has read it
+    const int buf = int(tag & 1u);
+    float4* w_local = reinterpret_cast<float4*>(v.region[rank] + v.params_off) + off4;
+    float4* g_local = reinterpret_cast<float4*>(v.region[rank] + v.grads_off[parity]) + off4;
+    const float lr = (lr_dev ? *lr_dev : lr_imm) / float(world);
+    const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x, nthreads = size_t(gridDim.x) * blockDim.x;
+    bool ok = true;
+
+    if (!two_shot) {
+        for (size_t i = tid; i < n4; i += nthreads) {
+            const float4 mine = g_local[i];
+#pragma unroll
+            for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++)
+                if (k < world && k != rank) ll::push4(ll::slot_ptr(c, k, buf, rank), i, mine, tag);
+        }
+        for (size_t i = tid; i < n4 && ok; i += nthreads) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++) {
+                if (k >= world) continue;
+                float4 t4;
+                if (k == rank) t4 = g_local[i];
+                else ok = ok && ll::poll4(ll::slot_ptr(c, rank, buf, k), i, tag, t4);
+                acc = k == 0 ? t4 : add4(acc, t4);
+            }
+            if (!ok) break;
+            if (op == kOpSgd) {
+                float4 w = w_local[i];
+                w.x -= lr * acc.x;
+                w.y -= lr * acc.y;
+                w.z -= lr * acc.z;
+                w.w -= lr * acc.w;
+                w_local[i] = w;
+            } else {
+                g_local[i] = acc;
+            }
+        }
+    } else {
+        // reduce-scatter: my part of shard s goes to rank s
+#pragma unroll
+        for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++) {
+            if (k >= world || k == rank) continue;
+            const size_t lo = n4 * size_t(k) / world, hi = n4 * size_t(k + 1) / world;
+            uint4* slot = ll::slot_ptr(c, k, buf, rank);
+            for (size_t i = lo + tid; i < hi; i += nthreads) ll::push4(slot, i - lo, g_local[i], tag);
+        }
+        const size_t lo = n4 * size_t(rank) / world, hi = n4 * size_t(rank + 1) / world;
+        const size_t dst_off = (op == kOpSgd) ? v.params_off : v.grads_off[parity];
+        for (size_t i = lo + tid; i < hi && ok; i += nthreads) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++) {
+                if (k >= world) continue;
+                float4 t4;
+                if (k == rank) t4 = g_local[i];
+                else ok = ok && ll::poll4(ll::slot_ptr(c, rank, buf, k), i - lo, tag, t4);
+                acc = k == 0 ? t4 : add4(acc, t4);
+            }
+            if (!ok) break;
+            float4 out = acc;
+            if (op == kOpSgd) {
+                out = w_local[i];
+                out.x -= lr * acc.x;
+                out.y -= lr * acc.y;
+                out.z -= lr * acc.z;
+                out.w -= lr * acc.w;
+            }
+#pragma unroll
+            for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++)
+                if (k < world) st_peer(reinterpret_cast<float4*>(v.region[k] + dst_off) + off4 + i, out);
+        }
+    }
+    if (!ok) atomicExch(v.errflag, 1u);
+    __syncthreads();  // the block's stores are issued; one release per peer publishes them
+    if (two_shot && threadIdx.x < world && int(threadIdx.x) != rank)
+        st_release_sys(wflag_ptr(v.region[threadIdx.x], ch, rank, int(blockIdx.x)), tag);
+    if (threadIdx.x == 0) {
+        const uint32_t prev = atomicAdd(&c.ctr->done, 1u);
+        if (prev == gridDim.x - 1) {  // last block of this rank: every block has read `calls`
+            c.ctr->done = 0;
+            c.ctr->calls = tag;
+            if (two_shot) {
+                c.ctr->wtag = tag;
+                c.ctr->wblocks = gridDim.x;
+            }
+        }
+    }
+}
+
+// Second half of the two-shot push algorithm, run by the CONSUMER of the result (the next step's forward, or the
+// host before it reads the parameters): wait until every peer's blocks have raised their flag for the last two-shot
+// call on channel `ch`.  One block.
+__global__ void __launch_bounds__(kCommThreads) ll_wait_weights_kernel(CommView v, int ch) {
+    const int rank = v.emulate ? int(blockIdx.y) : v.rank;
+    const ll::Channel c = make_channel(v, rank, ch);
+    const uint32_t wtag = c.ctr->wtag;
+    const int nb = int(c.ctr->wblocks);
+    if (wtag == 0) return;
+    for (int idx = threadIdx.x; idx < v.world * nb; idx += blockDim.x) {
+        const int src = idx / nb, b = idx % nb;
+        if (src == rank) continue;
+        const uint32_t* f = wflag_ptr(v.region[rank], ch, src, b);
+        const long long t0 = clock64();
+        while (int32_t(ld_acquire_sys(f) - wtag) < 0) {
+            if (clock64() - t0 > kSpinTimeoutCycles) {
+                atomicExch(v.errflag, 1u);
+                break;
+            }
+        }
+    }
+}
+
 int pick_blocks(size_t n4, int max_blocks, int per_thread = 4) {
     // ~4 float4 per thread per block before adding blocks: launch + flag latency dominates small slices.
     // (per_thread = 1 for a slice on the critical path: every extra trip of the loop is one more NVLink round trip,
@@ -305,19 +461,40 @@ struct b200cnn_comm {
     size_t flat_floats = 0;
     int algo = B200CNN_ALGO_AUTO;
     int parity = 0;
-    uint32_t* local = nullptr;  // seq counters + error flag
+    uint32_t* local = nullptr;  // seq counters + error flag + push-protocol counters
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_wait = nullptr;
     bool forked = false;
+    bool wait_pending = false;  // a wait kernel has been enqueued on `stream` and `ev_wait` recorded behind it
 };
 
 namespace {
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-int resolve_algo(const b200cnn_comm* c, int algo, size_t count, int op) {
+bool ll_enabled() {
+    static const bool on = [] {
+        const char* v = std::getenv("B200CNN_LL");  // B200CNN_LL=0: pull protocol only (A/B timing)
+        return !(v && v[0] == '0');
+    }();
+    return on;
+}
+
+int resolve_algo(const b200cnn_comm* c, int algo, size_t count, int op, int ch) {
     if (algo == B200CNN_ALGO_AUTO) algo = c->algo;
     if (c->view.world == 1) return B200CNN_ALGO_ONE_SHOT;
+    const size_t payload = ll::slot_bytes(ch) / 2;  // bytes of payload one source may push into one inbox slot
+    const size_t shard = (count / 4 + c->view.world - 1) / c->view.world * 16 + 16;
+    if (algo == B200CNN_ALGO_AUTO && ll_enabled()) {
+        // Push protocol wherever the slice fits an inbox: one-shot while every rank can afford to send the whole
+        // slice to everybody ((W-1) x 2 x bytes over its links), two-shot while a shard fits a slot.
+        const size_t bytes = count * sizeof(float);
+        if (bytes <= payload && bytes * size_t(c->view.world - 1) <= (448u << 10)) return B200CNN_ALGO_LL_ONE_SHOT;
+        if (shard <= payload && bytes <= (8u << 20)) return B200CNN_ALGO_LL_TWO_SHOT;
+    }
+    if (algo == B200CNN_ALGO_LL_ONE_SHOT && count * sizeof(float) > payload) algo = B200CNN_ALGO_LL_TWO_SHOT;
+    if (algo == B200CNN_ALGO_LL_TWO_SHOT && shard > payload) algo = B200CNN_ALGO_AUTO;  // too big for the inboxes
+    if (algo == B200CNN_ALGO_LL_ONE_SHOT || algo == B200CNN_ALGO_LL_TWO_SHOT) return algo;
     if (algo == B200CNN_ALGO_AUTO) {
         // Measured crossovers on 8xB200 (profiles/allreduce_sweep_w*.json and in-step runs): one-shot wins while
         // (W-1) x bytes of peer loads cost less than a second flag exchange; NVLS wins once the message is large
@@ -329,6 +506,7 @@ int resolve_algo(const b200cnn_comm* c, int algo, size_t count, int op) {
         else algo = B200CNN_ALGO_TWO_SHOT;
     }
     if (algo == B200CNN_ALGO_NVLS && !c->view.mc_region) algo = B200CNN_ALGO_TWO_SHOT;
+    if (algo == B200CNN_ALGO_AUTO) algo = B200CNN_ALGO_TWO_SHOT;
     // The in-place one-shot all-reduce keeps at most 4 float4 per thread in registers.
     if (op == kOpReduceOnly && algo == B200CNN_ALGO_ONE_SHOT &&
         count / 4 > size_t(kMaxBlocks) * kCommThreads * 4)
@@ -353,13 +531,54 @@ int launch(const CommView& v, int ranks_y, size_t off4, size_t n4, const float* 
     return 0;
 }
 
+int launch_ll(const CommView& v, int ranks_y, size_t off4, size_t n4, const float* lr_dev, float lr, int two_shot, int parity,
+              int op, int ch, int blocks, cudaStream_t st) {
+    const dim3 grid(blocks, ranks_y);
+#define B200CNN_LAUNCH_LL(W) ll_allreduce_kernel<W><<<grid, kCommThreads, 0, st>>>(v, off4, n4, lr_dev, lr, two_shot, parity, op, ch)
+    switch (v.world) {
+        case 2: B200CNN_LAUNCH_LL(2); break;
+        case 4: B200CNN_LAUNCH_LL(4); break;
+        case 8: B200CNN_LAUNCH_LL(8); break;
+        default: B200CNN_LAUNCH_LL(0); break;
+    }
+#undef B200CNN_LAUNCH_LL
+    B200CNN_CHECK_LAUNCH("ll_allreduce_sgd");
+    return 0;
+}
+
+int launch_ll_wait(const CommView& v, int ranks_y, int ch, cudaStream_t st) {
+    ll_wait_weights_kernel<<<dim3(1, ranks_y), kCommThreads, 0, st>>>(v, ch);
+    B200CNN_CHECK_LAUNCH("ll_wait_weights");
+    return 0;
+}
+
+// Grid of a push-protocol call: the push loop is store-issue bound, so a big slice gets all the blocks it is allowed;
+// a small one gets one float4 per thread (every extra trip of the poll loop is exposed latency).
+int pick_ll_blocks(size_t n4, int max_blocks, bool two_shot) {
+    if (max_blocks <= 0 || max_blocks > kLLMaxBlocks) max_blocks = two_shot ? 32 : 16;
+    size_t b = (n4 + kCommThreads - 1) / kCommThreads;
+    if (two_shot) b = (b + 3) / 4;
+    if (b < 1) b = 1;
+    if (b > size_t(max_blocks)) b = size_t(max_blocks);
+    return int(b);
+}
+
+// ch: push-protocol channel (ll.cuh) = which stream family this call is ordered on.  defer_wait: a two-shot push call
+// returns once THIS rank's shard is stored everywhere; the wait for the peers' shards is left to comm_wait_weights().
 int enqueue(b200cnn_comm* c, size_t offset, size_t count, const float* lr_dev, float lr, int algo, int parity, int op,
-            int root, int max_blocks, cudaStream_t st, int block_base = 0, int per_thread = 4) {
+            int root, int max_blocks, cudaStream_t st, int block_base = 0, int per_thread = 4, int ch = 0,
+            bool defer_wait = false) {
     if ((offset | count) & 3) return set_error(kInvalidValue, "comm: offset and count must be multiples of 4 floats");
     if (offset + count > c->flat_floats) return set_error(kInvalidValue, "comm: slice [%zu, %zu) outside the %zu-float buffer", offset, offset + count, c->flat_floats);
     if (parity != 0 && parity != 1) return set_error(kInvalidValue, "comm: parity must be 0 or 1");
-    algo = resolve_algo(c, algo, count, op);
+    algo = (op == kOpSgd || op == kOpReduceOnly) ? resolve_algo(c, algo, count, op, ch) : B200CNN_ALGO_ONE_SHOT;
     const size_t n4 = count / 4;
+    if (algo == B200CNN_ALGO_LL_ONE_SHOT || algo == B200CNN_ALGO_LL_TWO_SHOT) {
+        const bool two = algo == B200CNN_ALGO_LL_TWO_SHOT;
+        if (int rc = launch_ll(c->view, 1, offset / 4, n4, lr_dev, lr, two ? 1 : 0, parity, op, ch, pick_ll_blocks(n4, max_blocks, two), st)) return rc;
+        if (two && !defer_wait) return launch_ll_wait(c->view, 1, ch, st);
+        return 0;
+    }
     int blocks = pick_blocks(n4, max_blocks, per_thread);
     if (op == kOpReduceOnly && algo == B200CNN_ALGO_ONE_SHOT) {
         // registers hold the results across the barrier: make sure 4 per thread is enough
@@ -376,9 +595,8 @@ extern "C" size_t b200cnn_comm_grads_offset(size_t flat_floats, int parity) {
     const size_t buf = align_up(flat_floats * sizeof(float), 4096);
     return B200CNN_COMM_FLAG_BYTES + buf * size_t(1 + (parity ? 1 : 0));
 }
-extern "C" size_t b200cnn_comm_region_bytes(size_t flat_floats) {
-    return B200CNN_COMM_FLAG_BYTES + 3 * align_up(flat_floats * sizeof(float), 4096);
-}
+static size_t ll_offset(size_t flat_floats) { return B200CNN_COMM_FLAG_BYTES + 3 * align_up(flat_floats * sizeof(float), 4096); }
+extern "C" size_t b200cnn_comm_region_bytes(size_t flat_floats) { return ll_offset(flat_floats) + ll::kTotalBytes; }
 
 extern "C" b200cnn_comm* b200cnn_comm_create(int rank, int world, void* const* region_ptrs, void* multicast_ptr,
                                              size_t flat_floats) {
@@ -397,10 +615,12 @@ extern "C" b200cnn_comm* b200cnn_comm_create(int rank, int world, void* const* r
     c->view.params_off = b200cnn_comm_params_offset(flat_floats);
     c->view.grads_off[0] = b200cnn_comm_grads_offset(flat_floats, 0);
     c->view.grads_off[1] = b200cnn_comm_grads_offset(flat_floats, 1);
-    const size_t local_bytes = (kMaxBlocks + 16) * sizeof(uint32_t);
+    c->view.ll_off = ll_offset(flat_floats);
+    const size_t local_bytes = (kMaxBlocks + 16) * sizeof(uint32_t) + ll::kChannels * sizeof(ll::Counters);
     if (cudaMalloc(&c->local, local_bytes) != cudaSuccess || cudaMemset(c->local, 0, local_bytes) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_wait, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
         set_error(int(cudaGetLastError()), "comm_create: CUDA resource creation failed");
         delete c;
@@ -408,6 +628,7 @@ extern "C" b200cnn_comm* b200cnn_comm_create(int rank, int world, void* const* r
     }
     c->view.seq = c->local;
     c->view.errflag = c->local + kMaxBlocks;
+    c->view.ll_ctr = reinterpret_cast<ll::Counters*>(c->local + kMaxBlocks + 16);
     return c;
 }
 
@@ -415,6 +636,7 @@ extern "C" void b200cnn_comm_destroy(b200cnn_comm* c) {
     if (!c) return;
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->ev_wait) cudaEventDestroy(c->ev_wait);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->local) cudaFree(c->local);
     delete c;
@@ -430,7 +652,7 @@ extern "C" float* b200cnn_comm_grads(b200cnn_comm* c, int parity) {
     return reinterpret_cast<float*>(c->view.region[c->view.rank] + c->view.grads_off[parity ? 1 : 0]);
 }
 extern "C" int b200cnn_comm_set_algo(b200cnn_comm* c, int algo) {
-    if (algo < B200CNN_ALGO_AUTO || algo > B200CNN_ALGO_NVLS) return set_error(kInvalidValue, "comm_set_algo: unknown algorithm %d", algo);
+    if (algo < B200CNN_ALGO_AUTO || algo > B200CNN_ALGO_LL_TWO_SHOT) return set_error(kInvalidValue, "comm_set_algo: unknown algorithm %d", algo);
     if (algo == B200CNN_ALGO_NVLS && !c->view.mc_region) return set_error(kInvalidValue, "comm_set_algo: no multicast mapping on this communicator");
     c->algo = algo;
     return 0;
@@ -484,6 +706,39 @@ extern "C" int b200cnn_comm_emulate_allreduce_sgd(int world, void* const* region
                                                    seq_scratch, stream);
 }
 
+extern "C" int b200cnn_comm_wait_weights(b200cnn_comm* c, b200cnn_stream stream) {
+    if (c->view.world == 1) return 0;
+    for (int ch = 0; ch < 2; ch++)
+        if (int rc = launch_ll_wait(c->view, 1, ch, as_stream(stream))) return rc;
+    return 0;
+}
+
+extern "C" size_t b200cnn_comm_emulate_ll_scratch_bytes(int world) {
+    return size_t(world) * ll::kChannels * sizeof(ll::Counters) + 16;
+}
+
+extern "C" int b200cnn_comm_emulate_ll(int world, void* const* region_ptrs, size_t flat_floats, size_t offset, size_t count,
+                                       float lr, int two_shot, int parity, int blocks, int channel, int update, void* scratch,
+                                       b200cnn_stream stream) {
+    if (world < 2 || world > kMaxRanks || (offset | count) & 3 || offset + count > flat_floats || channel < 0 || channel > 1)
+        return set_error(kInvalidValue, "comm_emulate_ll: bad arguments");
+    if (blocks < 1 || blocks > kLLMaxBlocks || blocks * world > 148) return set_error(kInvalidValue, "comm_emulate_ll: blocks*world must fit one wave (<= 148)");
+    const size_t per_src = two_shot ? ((count / 4 + world - 1) / world * 16 + 16) : count * sizeof(float);
+    if (per_src > ll::slot_bytes(channel) / 2) return set_error(kInvalidValue, "comm_emulate_ll: slice does not fit the inbox of channel %d", channel);
+    CommView v{};
+    v.world = world;
+    v.emulate = 1;
+    for (int r = 0; r < kMaxRanks; r++) v.region[r] = static_cast<char*>(region_ptrs[r < world ? r : 0]);
+    v.params_off = b200cnn_comm_params_offset(flat_floats);
+    v.grads_off[0] = b200cnn_comm_grads_offset(flat_floats, 0);
+    v.grads_off[1] = b200cnn_comm_grads_offset(flat_floats, 1);
+    v.ll_off = ll_offset(flat_floats);
+    v.ll_ctr = static_cast<ll::Counters*>(scratch);
+    v.errflag = reinterpret_cast<uint32_t*>(static_cast<char*>(scratch) + size_t(world) * ll::kChannels * sizeof(ll::Counters));
+    if (int rc = launch_ll(v, world, offset / 4, count / 4, nullptr, lr, two_shot, parity, update ? kOpSgd : kOpReduceOnly, channel, blocks, as_stream(stream))) return rc;
+    return two_shot ? launch_ll_wait(v, world, channel, as_stream(stream)) : 0;
+}
+
 // ---- engine hooks ---------------------------------------------------------------------------
 namespace b200cnn {
 
@@ -497,7 +752,35 @@ int comm_allreduce_sgd_slice(b200cnn_comm* c, size_t offset, size_t count, const
         const int v = s ? std::atoi(s) : 16;
         return v < 1 ? 1 : v > kMaxBlocks / 2 ? kMaxBlocks / 2 : v;
     }();
-    return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, max_blocks, c->stream);
+    return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, max_blocks, c->stream, 0, 4, /*ch=*/0,
+                   /*defer_wait=*/true);
+}
+
+// Start of a step: the previous step's two-shot push calls stored their shards of the new weights into the peers and
+// left; this enqueues (on the communicator's stream, next to whatever `st` does first) the kernel that waits until
+// all peers' shards have landed HERE.  comm_weights_ready() then makes `st` wait for it — call it right before the
+// first kernel that reads parameters a bucket may have updated.
+int comm_begin_step(b200cnn_comm* c, cudaStream_t st) {
+    if (c->view.world == 1) return 0;
+    B200CNN_CUDA(cudaEventRecord(c->ev_fork, st));
+    B200CNN_CUDA(cudaStreamWaitEvent(c->stream, c->ev_fork, 0));
+    for (int ch = 0; ch < 2; ch++)
+        if (int rc = launch_ll_wait(c->view, 1, ch, c->stream)) return rc;
+    B200CNN_CUDA(cudaEventRecord(c->ev_wait, c->stream));
+    c->wait_pending = true;
+    c->forked = true;
+    return 0;
+}
+
+bool comm_update_is_deferred(const b200cnn_comm* c, size_t count, int ch) {
+    return c->view.world > 1 && resolve_algo(c, B200CNN_ALGO_AUTO, count, kOpSgd, ch) == B200CNN_ALGO_LL_TWO_SHOT;
+}
+
+int comm_weights_ready(b200cnn_comm* c, cudaStream_t st) {
+    if (!c->wait_pending) return 0;
+    B200CNN_CUDA(cudaStreamWaitEvent(st, c->ev_wait, 0));
+    c->wait_pending = false;
+    return 0;
 }
 
 // Same operation enqueued directly on `st` (no stream hop), on the second flag channel so it may overlap a
@@ -512,8 +795,9 @@ int comm_allreduce_sgd_inline(b200cnn_comm* c, size_t offset, size_t count, cons
         return s ? std::atoi(s) : 0;
     }();
     int algo = forced > 0 ? forced : B200CNN_ALGO_AUTO;
-    if (forced <= 0 && count * sizeof(float) <= (32u << 10)) algo = B200CNN_ALGO_ONE_SHOT;
-    return enqueue(c, offset, count, lr_dev, 0.0f, algo, c->parity, kOpSgd, 0, 16, st, kMaxBlocks / 2, /*per_thread=*/1);
+    if (forced <= 0 && !ll_enabled() && count * sizeof(float) <= (32u << 10)) algo = B200CNN_ALGO_ONE_SHOT;
+    return enqueue(c, offset, count, lr_dev, 0.0f, algo, c->parity, kOpSgd, 0, 16, st, kMaxBlocks / 2, /*per_thread=*/1, /*ch=*/1,
+                   /*defer_wait=*/true);
 }
 
 int comm_join(b200cnn_comm* c, cudaStream_t st) {
@@ -527,14 +811,14 @@ int comm_join(b200cnn_comm* c, cudaStream_t st) {
 // The last flag slot is reserved for exchanges done inside other kernels (phase 0 only, one-shot, no exit barrier:
 // gradients are double-buffered by step parity).
 void comm_tail_xchg(const b200cnn_comm* c, TailXchg* out) {
-    out->world = c->view.world;
-    out->rank = c->view.rank;
-    out->slot = kMaxBlocks - 1;
-    for (int r = 0; r < kMaxRanks; r++) out->region[r] = c->view.region[r];
+    out->chan.world = c->view.world;
+    out->chan.rank = c->view.rank;
+    out->chan.ch = 2;
+    for (int r = 0; r < kMaxRanks; r++) out->chan.region[r] = c->view.region[r];
+    out->chan.inbox_off = c->view.ll_off;
+    out->chan.ctr = c->view.ll_ctr + 2;
+    out->chan.errflag = c->view.errflag;
     out->params_off = c->view.params_off;
-    out->grads_off = c->view.grads_off[c->parity];
-    out->seq = c->view.seq + out->slot;
-    out->errflag = c->view.errflag;
 }
 
 float* comm_current_grads(b200cnn_comm* c) { return b200cnn_comm_grads(c, c->parity); }

@@ -1,6 +1,8 @@
-// Device side of TailXchg (comm.cuh): the flag protocol of allreduce_sgd.cu (per-slot sequence numbers that only
-// grow, st.release.sys after a CTA barrier, ld.acquire.sys polling, bounded wait) for a kernel that exchanges a few
-// hundred floats with its peers in its own last block instead of handing them to a separate collective kernel.
+// Device side of TailXchg (comm.cuh): a kernel that has just produced a few hundred floats (the weight gradient of
+// the first convolution, in the block that finishes last) all-reduces them with its peers ITSELF instead of handing
+// them to a separate collective kernel: compute + collective + update in one launch.  Push protocol of ll.cuh on
+// channel 2: every float is stored into every peer's inbox as an 8-byte {value, tag} packet, then the CTA polls its
+// own inbox — one one-way NVLink trip, no flag, no fence, no remote load.
 #pragma once
 #include <cstdint>
 
@@ -9,44 +11,29 @@
 namespace b200cnn {
 namespace xchg {
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ float ld_peer(const float* p) {
-    float v;
-    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
-    return v;
-}
-// Same layout as flag_ptr() in allreduce_sgd.cu: [slot][phase][source rank] words at the start of a region.
-__device__ __forceinline__ uint32_t* flag_ptr(char* region, int slot, int phase, int src) {
-    return reinterpret_cast<uint32_t*>(region) + (slot * 2 + phase) * B200CNN_COMM_MAX_RANKS + src;
-}
-
-// Every thread of the CTA calls this after the CTA's results are stored in this rank's gradient buffer.  On return
-// every peer's results of the same step are stored too (and visible).  Returns the sequence number to be written
-// back to *x.seq by ONE thread once the CTA is done with the exchange.
-__device__ __forceinline__ uint32_t all_ranks_ready(const TailXchg& x) {
-    const uint32_t seq = *x.seq + 1;
-    __syncthreads();
-    if (int(threadIdx.x) < x.world && int(threadIdx.x) != x.rank) {
-        const int peer = threadIdx.x;
-        st_release_sys(flag_ptr(x.region[peer], x.slot, 0, x.rank), seq);
-        const uint32_t* mine = flag_ptr(x.region[x.rank], x.slot, 0, peer);
-        const long long t0 = clock64();
-        while (int32_t(ld_acquire_sys(mine) - seq) < 0) {
-            if (clock64() - t0 > 4000000000ll) {  // ~2 s: raise the communicator's error flag instead of hanging
-                atomicExch(x.errflag, 1u);
-                break;
-            }
+// Called by EVERY thread of ONE CTA per rank.  Thread t < n contributes `mine` (element t of the slice) and receives in
+// `sum` the total over ranks, added in rank order (bitwise identical on every rank).  Returns false for a thread
+// whose peer never showed up (~2 s; the communicator's error flag is raised and the caller must skip its update).
+__device__ __forceinline__ bool allreduce_small(const TailXchg& x, int t, int n, float mine, float& sum) {
+    const ll::Channel& c = x.chan;
+    const uint32_t tag = c.ctr->calls + 1;
+    const int buf = int(tag & 1u);
+    bool ok = true;
+    if (t < n) {
+        for (int k = 0; k < c.world; k++)
+            if (k != c.rank) ll::push1(ll::slot_ptr(c, k, buf, c.rank), size_t(t), mine, tag);
+        float acc = 0.f;
+        for (int k = 0; k < c.world && ok; k++) {
+            float v = mine;
+            if (k != c.rank) ok = ll::poll1(ll::slot_ptr(c, c.rank, buf, k), size_t(t), tag, v);
+            acc = k == 0 ? v : acc + v;
         }
+        sum = acc;
+        if (!ok) atomicExch(c.errflag, 1u);
     }
-    __syncthreads();
-    return seq;
+    __syncthreads();  // every thread has read the call counter
+    if (threadIdx.x == 0) c.ctr->calls = tag;
+    return ok;
 }
 
 }  // namespace xchg

@@ -6,9 +6,11 @@
 // a batch, optionally captured as one CUDA graph so a step costs one launch on the host.
 //
 // Memory: all parameters live in ONE flat fp32 buffer and all gradients in another, each tensor
-// starting on a 128-byte boundary.  The single-GPU update is one kernel over the flat buffer; the
-// data-parallel path binds NVLink-mapped symmetric buffers (b200cnn_engine_bind_buffers) and runs the
-// fused all-reduce + SGD kernel per layer slice instead.
+// starting on a 128-byte boundary.  Single GPU: the update is fused into backward (the upper layers on the
+// side stream as soon as nothing reads their weights any more, the first layer inside its own weight-gradient
+// kernel).  Data parallel: the buffers live in the communicator's NVLink-mapped region and the fused
+// all-reduce + SGD runs per BUCKET of adjacent layer slices (>= 512 KiB, or whatever is left at the first
+// layer), each launched as soon as its last gradient exists.
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -86,6 +88,7 @@ struct b200cnn_engine {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
     int host_slot = 0;
+    int wait_layer = 1;       // data parallel: first layer whose parameters a deferred (two-shot push) update may write
     bool last_fast = false;   // layout of layer 1's activations in the last forward (NHWC when true)
     bool fast_chain = false;  // conv(C_in=1) -> tc conv3x3 -> FC pattern: NHWC activations + tcgen05 convolutions
 };
@@ -143,6 +146,10 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
         const void* in = (li == 1) ? images : static_cast<const void*>(p.a);
         const int in_u8 = (li == 1) ? is_u8 : 0;
         int rc = 0;
+        // Data parallel: from this layer on the parameters may have been written by the peers (two-shot push of the
+        // previous step); the wait for their arrival was enqueued on the communicator's stream at the start of the step.
+        if (e->comm && int(li) >= e->wait_layer && l.nw > 0)
+            if ((rc = comm_weights_ready(e->comm, st))) return rc;
         switch (l.d.type) {
             case B200CNN_LAYER_CONV: {
                 const b200cnn_conv_shape s = conv_shape(p, l, batch);
@@ -225,8 +232,8 @@ int enqueue_sgd_range(b200cnn_engine* e, size_t begin, size_t end, cudaStream_t 
 
 static bool fused_tail_requested() {
     static const bool on = [] {
-        const char* v = getenv("B200CNN_FUSED_TAIL");
-        return v && v[0] == '1';
+        const char* v = getenv("B200CNN_FUSED_TAIL");  // B200CNN_FUSED_TAIL=0: separate collective kernel after backward
+        return !(v && v[0] == '0');
     }();
     return on;
 }
@@ -239,10 +246,10 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
     cudaStream_t side = e->side;
     e->bucket_lo = e->bucket_hi = -1;
     e->tail_lo = e->tail_hi = -1;
-    // Opt-in (B200CNN_FUSED_TAIL=1 with B200CNN_TC_C1=1, not validated on several GPUs yet — NOTES_NEXT.md): the first
-    // convolution's weight-gradient kernel all-reduces its 160 numbers itself in its last block and the second
-    // convolution's slice goes out on the side stream as soon as it exists, so no collective kernel is left on the
-    // main stream after the last kernel of backward.
+    // Data parallel, tensor-core chain: the first convolution's weight-gradient kernel all-reduces its 160 numbers
+    // itself in its last block (push protocol, csrc/comm/xchg_device.cuh) and the second convolution's slice goes
+    // out on the side stream as soon as it exists, so no collective kernel is left on the main stream after the last
+    // kernel of backward.
     TailXchg xchg;
     bool fused_tail = false;
     if (e->comm && fast && fused_tail_requested() && tc_conv1_bwd_weight_enabled() && is_u8 && L.size() > 3 &&
@@ -250,7 +257,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
         const b200cnn_conv_shape s1 = conv_shape(L[0], L[1], batch);
         if (tc_conv1_bwd_weight_supported(&s1, nhwc_bwd_weight_chunks(batch, nullptr))) {
             comm_tail_xchg(e->comm, &xchg);
-            fused_tail = xchg.world > 1;
+            fused_tail = xchg.world() > 1;
         }
     }
     for (size_t li = L.size() - 1; li >= 1; li--) {
@@ -294,6 +301,8 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
                                           fuse ? e->params + l.w_off : nullptr, fuse ? e->params + l.b_off : nullptr, e->lr_dev,
                                           xc ? &xchg : nullptr, long(l.w_off), long(l.b_off));
             }
+            else if (b200cnn_conv2d_bwd_weight_scratch_bytes(&s) > e->scratch_bytes)
+                rc = set_error(kInvalidValue, "engine: weight-gradient partial sums of layer %zu do not fit the scratch buffer", li);
             else
                 rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0,
                                               li == 1 ? e->scratch1 : e->scratch, &s, ws);
@@ -428,8 +437,13 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
                 l.nw = long(l.d.depth) * p.d.depth * l.d.k * l.d.k;
                 l.nb = l.d.depth;
                 l.act = B200CNN_ACT_RELU;
+                // The number of partial sums is NOT monotonic in the batch (ceil(n / ceil(n / 296)): 296 chunks at
+                // n = 296, 149 at n = 297), so size the scratch for the worst legal batch, not for max_batch.
                 b200cnn_conv_shape s = conv_shape(p, l, max_batch);
-                scratch_bytes = std::max(scratch_bytes, b200cnn_conv2d_bwd_weight_scratch_bytes(&s));
+                for (int n = 1; n <= max_batch; n++) {
+                    s.n = n;
+                    scratch_bytes = std::max(scratch_bytes, b200cnn_conv2d_bwd_weight_scratch_bytes(&s));
+                }
             } else if (l.d.type == B200CNN_LAYER_FULL) {
                 l.nw = long(l.nnodes) * p.nnodes;
                 l.nb = l.nnodes;
@@ -463,7 +477,8 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
                         nhwc_bwd_weight_supported(&s1, 1) && nhwc_bwd_weight_supported(&s2, 0) && s1.oc % 16 == 0 &&
                         tc_linear_bwd_data_supported(max_batch, e->layers[3].nnodes, e->layers[2].nnodes, e->layers[3].ld);
         if (e->fast_chain) {
-            const size_t chunks = size_t(nhwc_bwd_weight_chunks(max_batch, nullptr));
+            size_t chunks = 0;  // worst case over every legal batch (same non-monotonic shape as above, period 148)
+            for (int n = 1; n <= max_batch; n++) chunks = std::max(chunks, size_t(nhwc_bwd_weight_chunks(n, nullptr)));
             scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[2].nw + e->layers[2].nb) * sizeof(float) + 128);
             scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float) + 128);
         }
@@ -589,6 +604,10 @@ extern "C" int b200cnn_engine_set_params(b200cnn_engine* e, const float* dense_h
     return dense_transfer(e, e->params ? e->params : b200cnn_engine_params(e), const_cast<float*>(dense_host), true);
 }
 extern "C" int b200cnn_engine_get_params(b200cnn_engine* e, float* dense_host) {
+    if (e->comm) {  // data parallel: parts of the last update are written by the peers; wait until they are here
+        if (int rc = b200cnn_comm_wait_weights(e->comm, nullptr)) return rc;
+        B200CNN_CUDA(cudaDeviceSynchronize());
+    }
     return dense_transfer(e, b200cnn_engine_params(e), dense_host, false);
 }
 extern "C" int b200cnn_engine_get_grads(b200cnn_engine* e, float* dense_host) {
@@ -603,6 +622,8 @@ extern "C" int b200cnn_engine_forward(b200cnn_engine* e, const void* images, int
     e->last_images = images;
     e->last_is_u8 = x_is_u8;
     e->last_batch = batch;
+    if (e->comm)  // the peers' shards of the last update must have landed before anything reads the parameters
+        if (int rc = b200cnn_comm_wait_weights(e->comm, stream)) return rc;
     return enqueue_forward(e, images, x_is_u8, labels, batch, as_stream(stream), nullptr);
 }
 
@@ -628,6 +649,8 @@ extern "C" int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream st
 static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
                         cudaStream_t st, int* launches, bool update = true) {
     const bool head = use_head(e, batch);
+    if (e->comm)
+        if (int rc = comm_begin_step(e->comm, st)) return rc;
     if (!head) {
         if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches)) return rc;
     } else {
@@ -818,5 +841,27 @@ extern "C" int b200cnn_engine_attach_comm(b200cnn_engine* e, b200cnn_comm* comm)
     e->grads = b200cnn_comm_grads(comm, 0);
     e->own_buffers = false;
     e->comm = comm;
+    // Which layers can a deferred update touch?  Replay the bucketing of layer_grads_ready(): every bucket launched
+    // before the last one may be a two-shot push call (peers write this rank's parameters after the call returns);
+    // the last bucket is one only if it is too big for the one-shot form.
+    e->wait_layer = int(e->layers.size());
+    long lo = -1, hi = -1;
+    int first_param_layer = 1;
+    for (size_t li = 1; li < e->layers.size(); li++)
+        if (e->layers[li].nw > 0) {
+            first_param_layer = int(li);
+            break;
+        }
+    for (size_t li = e->layers.size() - 1; li >= 1; li--) {
+        const EngineLayer& l = e->layers[li];
+        if (l.nw == 0) continue;
+        const long begin = l.w_off, end = l.b_off + long(round_up(size_t(l.nb), kAlignFloats));
+        lo = lo < 0 ? begin : std::min(lo, begin);
+        hi = std::max(hi, end);
+        const bool last = int(li) == first_param_layer;
+        if (!last && hi - lo < kBucketFloats) continue;
+        if (comm_update_is_deferred(comm, size_t(hi - lo), last ? 1 : 0)) e->wait_layer = std::min(e->wait_layer, int(li));
+        lo = hi = -1;
+    }
     return 0;
 }

@@ -1,8 +1,8 @@
 // Weight gradient of the FIRST convolution (1 -> 16 channels, 3x3 / stride 2 / pad 1, 28x28 uint8 image -> 14x14)
-// on the tensor cores.  OPT-IN (B200CNN_TC_C1=1): written at the end of a round, it got one run on hardware
-// (tools/diag_c1_tc.py: correct at batch 256 / 2 / 7 / 64, 5.7 us per launch against 8.2 us for the CUDA-core kernel
-// in conv_nhwc.cu) but the GPU test-suite and the in-step timing with it enabled are still owed, so the CUDA-core
-// kernel stays the default (NOTES_NEXT.md, item 1).  Its index algebra is pinned by tests/test_c1_tc_layout.py.
+// on the tensor cores.  Default path of the engine's tensor-core chain (B200CNN_TC_C1=0 falls back to the CUDA-core
+// kernel in conv_nhwc.cu): 5.7 us per launch against 8.2 us for that kernel (tools/diag_c1_tc.py), the whole GPU
+// test-suite passes with it, direct value test in tests/test_gpu_ops.py.  Its index algebra is pinned by
+// tests/test_c1_tc_layout.py.
 //
 //     dW[oc][tap] = sum over (n, pixel) of dz[n][pixel][oc] * x[n][patch(pixel, tap)] / 255,   db[oc] = sum dz
 //
@@ -187,8 +187,9 @@ tc_conv1_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_dz, C1Args a
         red[pt * kNOut + jo] = acc;
     }
     __syncthreads();
+    float acc = 0.f;
     if (t < kNOut) {
-        float acc = red[t];
+        acc = red[t];
         for (int sl = 1; sl < kParts; sl++) acc += red[sl * kNOut + t];
         float* dst = t < kNW ? (a.dw ? a.dw + t : nullptr) : (a.db ? a.db + (t - kNW) : nullptr);
         if (dst) {
@@ -200,18 +201,15 @@ tc_conv1_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_dz, C1Args a
             *wdst -= *a.lr_dev * acc;
         }
     }
-    if (a.xc.world > 1) {
-        // compute + collective in one kernel: conv1's gradient never waits for a separate all-reduce launch
-        const uint32_t seq = xchg::all_ranks_ready(a.xc);
-        if (t < kNOut) {
+    if (a.xc.world() > 1) {
+        // compute + collective + update in one kernel: conv1's gradient never waits for a separate all-reduce launch
+        float s = 0.f;
+        const bool ok = xchg::allreduce_small(a.xc, t, kNOut, acc, s);
+        if (t < kNOut && ok) {
             const size_t idx = size_t(t < kNW ? a.w_off + t : a.b_off + (t - kNW));
-            float s = 0.f;
-            for (int k = 0; k < a.xc.world; k++)
-                s += xchg::ld_peer(reinterpret_cast<const float*>(a.xc.region[k] + a.xc.grads_off) + idx);
-            float* w = reinterpret_cast<float*>(a.xc.region[a.xc.rank] + a.xc.params_off) + idx;
-            *w -= (*a.lr_dev / float(a.xc.world)) * s;
+            float* w = reinterpret_cast<float*>(a.xc.chan.region[a.xc.chan.rank] + a.xc.params_off) + idx;
+            *w -= (*a.lr_dev / float(a.xc.world())) * s;
         }
-        if (t == 0) *a.xc.seq = seq;
     }
 }
 
@@ -219,8 +217,8 @@ tc_conv1_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_dz, C1Args a
 
 bool tc_conv1_bwd_weight_enabled() {
     static const bool on = [] {
-        const char* v = getenv("B200CNN_TC_C1");
-        return v && v[0] == '1';
+        const char* v = getenv("B200CNN_TC_C1");  // B200CNN_TC_C1=0: CUDA-core kernel of conv_nhwc.cu (A/B timing)
+        return !(v && v[0] == '0');
     }();
     return on && current_backend() != B200CNN_BACKEND_SIMT;
 }
@@ -234,7 +232,7 @@ bool tc_conv1_bwd_weight_supported(const b200cnn_conv_shape* s, int max_partials
 int tc_conv1_bwd_weight(const uint8_t* x, const float* dz_nhwc, float* dw, float* db, int accumulate, float* partials,
                         unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st, float* sgd_w, float* sgd_b,
                         const float* lr_dev, const TailXchg* xchg, long w_off, long b_off) {
-    if (xchg && xchg->world > 1 && (accumulate || sgd_w || !lr_dev || !dw || !db))
+    if (xchg && xchg->world() > 1 && (accumulate || sgd_w || !lr_dev || !dw || !db))
         return set_error(kInvalidValue, "tc_conv1_bwd_weight: the in-kernel all-reduce needs dw/db in the gradient buffer, no accumulation, no local update");
     CUtensorMap tm;
     const uint64_t dims[2] = {32, uint64_t(s->n) * kPairs};

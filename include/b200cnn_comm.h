@@ -11,11 +11,16 @@
  *
  * Memory model: each rank owns one "region" of device memory that every other rank has mapped
  * (CUDA IPC, CUDA VMM or torch symmetric memory — the library only needs the pointers):
- *     [ flags 16 KiB | params | grads[0] | grads[1] ]
+ *     [ flags 16 KiB | params | grads[0] | grads[1] | push-protocol inboxes (36 MiB) ]
  * Gradients are double-buffered by step parity, so a rank may start the next step's backward
  * while slower peers are still reading the previous step's gradients, and no trailing barrier is
  * needed.  Cross-GPU ordering uses monotonically increasing sequence numbers in the flag words
- * (st.release.sys / ld.acquire.sys); nothing is ever reset.
+ * (st.release.sys / ld.acquire.sys) or, in the push protocol, a tag inside every 8-byte packet;
+ * nothing is ever reset.
+ *
+ * Ordering contract: all calls of one communicator that use the same push channel must be ordered
+ * with respect to each other (same stream, or streams ordered by events) and made in the same order
+ * on every rank.  The stand-alone calls below all use channel 0.
  */
 #ifndef B200CNN_COMM_H
 #define B200CNN_COMM_H
@@ -35,7 +40,11 @@ enum {
     B200CNN_ALGO_AUTO = 0,
     B200CNN_ALGO_ONE_SHOT = 1, /* every rank reads all peers' full slice; best for small messages */
     B200CNN_ALGO_TWO_SHOT = 2, /* reduce-scatter + the owner writes UPDATED WEIGHTS to all peers */
-    B200CNN_ALGO_NVLS = 3      /* two-shot through the switch: multimem.ld_reduce + multimem.st */
+    B200CNN_ALGO_NVLS = 3,     /* two-shot through the switch: multimem.ld_reduce + multimem.st */
+    /* Push protocol (csrc/comm/ll.cuh): producers store {payload, tag} packets into the consumers' inboxes and the
+     * consumers poll their own memory - one one-way NVLink trip, no flag exchange, no fence, no remote load. */
+    B200CNN_ALGO_LL_ONE_SHOT = 4, /* everybody pushes the whole slice to everybody; slices up to an inbox slot */
+    B200CNN_ALGO_LL_TWO_SHOT = 5  /* push shard s to rank s, the owner stores the UPDATED WEIGHTS into every peer */
 };
 
 #define B200CNN_COMM_MAX_RANKS 8
@@ -58,8 +67,10 @@ int b200cnn_comm_world(const b200cnn_comm* c);
 int b200cnn_comm_has_multicast(const b200cnn_comm* c);
 float* b200cnn_comm_params(b200cnn_comm* c);
 float* b200cnn_comm_grads(b200cnn_comm* c, int parity);
-/* Algorithm used by the engine's bucket launches.  AUTO picks by measured crossover: one-shot up to 4 MiB / 256 KiB /
- * 8 KiB at world 2 / 4 / 8, NVLS from 8 MiB when a multicast mapping exists, two-shot in between. */
+/* Algorithm used by the engine's bucket launches.  AUTO: push one-shot while (world-1) x bytes <= 448 KiB, push
+ * two-shot while a 1/world shard fits an inbox slot (1 MiB) and the slice is <= 8 MiB; beyond that the pull kernels by
+ * measured crossover (NVLS from 8 MiB when a multicast mapping exists, else two-shot).  B200CNN_LL=0 in the
+ * environment removes the push algorithms from AUTO. */
 int b200cnn_comm_set_algo(b200cnn_comm* c, int algo);
 /* 0 if no kernel of this communicator ever timed out waiting for a peer; the kernels give up after
  * ~2 s instead of hanging the GPU. */
@@ -79,6 +90,10 @@ int b200cnn_comm_allreduce(b200cnn_comm* c, size_t offset, size_t count, int alg
 int b200cnn_comm_broadcast_params(b200cnn_comm* c, int root, b200cnn_stream stream);
 /* Device-side barrier across ranks. */
 int b200cnn_comm_barrier(b200cnn_comm* c, b200cnn_stream stream);
+/* Enqueue the wait for the peers' halves of the last LL_TWO_SHOT updates (a stand-alone b200cnn_comm_allreduce_sgd
+ * already includes it; the engine defers it to the start of the next step).  Call it, then synchronise, before
+ * reading parameters on the host after training through an engine. */
+int b200cnn_comm_wait_weights(b200cnn_comm* c, b200cnn_stream stream);
 
 /* Let an engine run its parameters / gradients inside the communicator's region and launch the
  * fused update per layer, overlapped with the rest of backward. */
@@ -103,6 +118,14 @@ int b200cnn_comm_emulate_allreduce_sgd(int world, void* const* region_ptrs, size
 int b200cnn_comm_emulate_allreduce_sgd_slot(int world, void* const* region_ptrs, size_t flat_floats, size_t offset,
                                             size_t count, float lr, int algo, int parity, int blocks, int slot_base,
                                             uint32_t* seq_scratch, b200cnn_stream stream);
+
+/* Test hook for the push protocol, same idea: `world` virtual ranks in one launch.  scratch: zeroed device memory of
+ * b200cnn_comm_emulate_ll_scratch_bytes(world) bytes, kept between calls (call counters + error word at its end).
+ * update != 0: all-reduce + SGD; 0: all-reduce into grads[parity]. */
+size_t b200cnn_comm_emulate_ll_scratch_bytes(int world);
+int b200cnn_comm_emulate_ll(int world, void* const* region_ptrs, size_t flat_floats, size_t offset, size_t count, float lr,
+                            int two_shot, int parity, int blocks, int channel, int update, void* scratch,
+                            b200cnn_stream stream);
 
 #ifdef __cplusplus
 }

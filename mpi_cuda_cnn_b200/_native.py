@@ -34,7 +34,7 @@ class LayerDesc(C.Structure):
 LAYER_INPUT, LAYER_FULL, LAYER_CONV, LAYER_POOL = 0, 1, 2, 3
 ACT_NONE, ACT_TANH, ACT_RELU = 0, 1, 2
 BACKEND_AUTO, BACKEND_SIMT, BACKEND_TCGEN05 = 0, 1, 2
-ALGO_AUTO, ALGO_ONE_SHOT, ALGO_TWO_SHOT, ALGO_NVLS = 0, 1, 2, 3
+ALGO_AUTO, ALGO_ONE_SHOT, ALGO_TWO_SHOT, ALGO_NVLS, ALGO_LL_ONE_SHOT, ALGO_LL_TWO_SHOT = 0, 1, 2, 3, 4, 5
 
 
 def build(targets=("cpu", "cuda"), quiet=True):
@@ -183,6 +183,9 @@ def cuda():
     _sig(lib, "b200cnn_comm_allreduce", i, vp, sz, sz, i, i, i, vp)
     _sig(lib, "b200cnn_comm_broadcast_params", i, vp, i, vp)
     _sig(lib, "b200cnn_comm_barrier", i, vp, vp)
+    _sig(lib, "b200cnn_comm_wait_weights", i, vp, vp)
+    _sig(lib, "b200cnn_comm_emulate_ll_scratch_bytes", sz, i)
+    _sig(lib, "b200cnn_comm_emulate_ll", i, i, C.POINTER(vp), sz, sz, sz, f, i, i, i, i, i, vp, vp)
     _sig(lib, "b200cnn_comm_emulate_allreduce_sgd", i, i, C.POINTER(vp), sz, sz, sz, f, i, i, i, vp, vp)
     _sig(lib, "b200cnn_comm_emulate_allreduce_sgd_slot", i, i, C.POINTER(vp), sz, sz, sz, f, i, i, i, i, vp, vp)
     _sig(lib, "b200cnn_ipc_alloc", vp, sz)

@@ -48,7 +48,7 @@ def _gpu_parser(dp):
     if dp:
         ap.add_argument("-np", "--np", type=int, default=0)
         ap.add_argument("--update", default="fused", choices=["fused", "nccl"])
-        ap.add_argument("--algo", default="auto", choices=["auto", "one_shot", "two_shot", "nvls"])
+        ap.add_argument("--algo", default="auto", choices=["auto", "one_shot", "two_shot", "nvls", "ll_one_shot", "ll_two_shot"])
     return ap
 
 
@@ -106,8 +106,13 @@ def _train_gpu(args, rank=0, world=1, device=None, trainer=None):
         engine.init_params(seed=args.seed)
     else:
         engine = trainer.engine
-    if args.load and rank == 0:
-        engine.set_params(np.fromfile(args.load, dtype=np.float32))
+    if args.load:
+        # Rank 0 reads the checkpoint, then EVERY replica gets a copy (the trainer's constructor has already
+        # broadcast the seed initialisation; loading on rank 0 alone would leave the other ranks on it).
+        if rank == 0:
+            engine.set_params(np.fromfile(args.load, dtype=np.float32))
+        if trainer is not None:
+            trainer.sync_params(0)
     train_size = len(tx)
     shard = train_size // world  # contiguous shard per rank, remainder dropped (cnnmpi.c:457-458)
     start, end = shard * rank, shard * (rank + 1)
@@ -137,13 +142,18 @@ def _train_gpu(args, rank=0, world=1, device=None, trainer=None):
                     trainer.train_step(xs, ys, args.rate, use_graph=not args.no_graph)
                 step += 1
                 seen += B
-                if rank == 0 and seen > next_log:
-                    m = engine.read_metrics()
-                    engine.reset_metrics()
-                    if m["count"] > 0:
-                        print(f"i={seen - B}, error={m['mse_sum'] / m['count']:.4f}", file=sys.stderr)
+                if seen > next_log:
+                    if trainer is not None:
+                        trainer.check_comm()  # a peer that never showed up must fail the run, not corrupt it silently
+                    if rank == 0:
+                        m = engine.read_metrics()
+                        engine.reset_metrics()
+                        if m["count"] > 0:
+                            print(f"i={seen - B}, error={m['mse_sum'] / m['count']:.4f}", file=sys.stderr)
                     next_log += max(args.log_every, B)
         stream.synchronize()
+        if trainer is not None:
+            trainer.check_comm()
         dt = time.perf_counter() - t0
         if rank == 0 and args.timing and step:
             print(f"train_images_per_sec={step * B * world / dt:.1f} ({step * B * world} samples, {world} GPU(s), {dt:.3f} s)", file=sys.stderr)

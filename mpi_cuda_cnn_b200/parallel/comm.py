@@ -8,7 +8,8 @@ from .. import _native as N
 from ..engine import _tensor_from_ptr
 from .symm import Region
 
-_ALGO = {"auto": N.ALGO_AUTO, "one_shot": N.ALGO_ONE_SHOT, "two_shot": N.ALGO_TWO_SHOT, "nvls": N.ALGO_NVLS}
+_ALGO = {"auto": N.ALGO_AUTO, "one_shot": N.ALGO_ONE_SHOT, "two_shot": N.ALGO_TWO_SHOT, "nvls": N.ALGO_NVLS,
+         "ll_one_shot": N.ALGO_LL_ONE_SHOT, "ll_two_shot": N.ALGO_LL_TWO_SHOT}
 
 
 class FusedComm:
@@ -63,6 +64,10 @@ class FusedComm:
 
     def barrier(self, stream=None):
         N.check(self.lib.b200cnn_comm_barrier(self.handle, self._st(stream)), "comm_barrier")
+
+    def wait_weights(self, stream=None):
+        """Enqueue the wait for the peers' shares of the last two-shot push updates (see include/b200cnn_comm.h)."""
+        N.check(self.lib.b200cnn_comm_wait_weights(self.handle, self._st(stream)), "comm_wait_weights")
 
     def error(self):
         return self.lib.b200cnn_comm_error(self.handle)

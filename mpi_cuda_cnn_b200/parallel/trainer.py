@@ -24,19 +24,36 @@ class DataParallelTrainer:
         self.comm = None
         if mode == "fused":
             self.comm = FusedComm(self.engine.flat_floats, rank, world, self.device, prefer=prefer_region)
+            if algo == "nvls" and not self.comm.has_multicast:
+                if rank == 0:
+                    print("[b200cnn] no NVLS multicast mapping on this box: using the two-shot P2P kernel instead")
+                algo = "two_shot"
             if algo != "auto":
                 self.comm.set_algo(algo)
             self.engine.attach_comm(self.comm)
         # Same seed everywhere AND an explicit broadcast of rank 0's parameters.
         self.engine.init_params(seed=seed)
-        if world > 1:
-            if self.comm is not None:
-                self.comm.broadcast_params(0)
-            else:
-                flat = self.flat_params()
-                dist.broadcast(flat, src=0)
-            torch.cuda.synchronize()
-            dist.barrier()
+        self.sync_params(0)
+
+    def sync_params(self, root=0):
+        """Make every replica a copy of rank ``root``'s parameters (over NVLink on the fused path).  Called after the
+        initialisation and again after ANY rank-local change of the parameters, e.g. a checkpoint loaded on rank 0
+        (the reference never synchronises its replicas at all: SURVEY D7)."""
+        if self.world <= 1:
+            return
+        torch.cuda.synchronize()
+        dist.barrier()  # nobody is still training on the old parameters, root's new ones are in place
+        if self.comm is not None:
+            self.comm.broadcast_params(root)
+        else:
+            dist.broadcast(self.flat_params(), src=root)
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    def check_comm(self):
+        """Raise if a kernel of the fused communicator ever gave up waiting for a peer (it then skipped its update)."""
+        if self.comm is not None and self.comm.error():
+            raise RuntimeError(f"rank {self.rank}: the fused communicator timed out waiting for a peer; the replicas are no longer in sync")
 
     def flat_params(self):
         from ..engine import _tensor_from_ptr

@@ -13,14 +13,21 @@ _QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,c
 class ClockSampler:
     """Samples SM clock and throttle reasons in a background thread while a timed region runs.
 
-    NVML (a ~1 ms call) when available, else `nvidia-smi` (tens of ms per sample)."""
+    NVML (a ~1 ms call) when available, else `nvidia-smi` (tens of ms per sample).
+
+    Construct it (NVML init, handle lookup: milliseconds, and different on every rank) and enter it BEFORE the barrier
+    that precedes a timed region, never between the barrier and the first event.  `begin()` / `end()` mark the timed
+    window with host timestamps; `summary()` then reports only the samples taken inside it.  `sample_now()` takes one
+    sample on the calling thread (NVML releases the GIL; call it right after the timed launches have been enqueued,
+    while the GPU is still working through them) so that even a 1 ms region has a sample taken under load."""
 
     _REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown"}
 
     def __init__(self, gpu_index=0, period_s=0.002):
         self.gpu_index = gpu_index
         self.period_s = period_s
-        self.samples = []  # (sm_mhz, sm_max_mhz, set(reasons))
+        self.samples = []  # (sm_mhz, sm_max_mhz, set(reasons), host time)
+        self._t0 = self._t1 = None
         self._stop = threading.Event()
         self._thread = None
         self._nvml = None
@@ -50,7 +57,7 @@ class ClockSampler:
             mask = int(n.nvmlDeviceGetCurrentClocksEventReasons(self._handle))
         except Exception:
             mask = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self._handle))
-        self.samples.append((sm, self._max, {name for bit, name in self._REASONS.items() if mask & bit}))
+        self.samples.append((sm, self._max, {name for bit, name in self._REASONS.items() if mask & bit}, time.perf_counter()))
 
     def _sample_smi(self):
         out = subprocess.run(["nvidia-smi", f"--id={self.gpu_index}", f"--query-gpu={_QUERY}", "--format=csv,noheader,nounits"],
@@ -59,15 +66,25 @@ class ClockSampler:
             return
         f = [v.strip() for v in out.splitlines()[0].split(",")]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        self.samples.append((float(f[0]), float(f[1]), {n for n, v in zip(names, f[3:7]) if v.lower().startswith("active")}))
+        self.samples.append((float(f[0]), float(f[1]), {n for n, v in zip(names, f[3:7]) if v.lower().startswith("active")},
+                             time.perf_counter()))
+
+    def sample_now(self):
+        try:
+            self._sample_nvml() if self._nvml else self._sample_smi()
+        except Exception:
+            pass
 
     def _poll(self):
         while not self._stop.is_set():
-            try:
-                self._sample_nvml() if self._nvml else self._sample_smi()
-            except Exception:
-                pass
+            self.sample_now()
             self._stop.wait(self.period_s)
+
+    def begin(self):
+        self._t0 = time.perf_counter()
+
+    def end(self):
+        self._t1 = time.perf_counter()
 
     def __enter__(self):
         self._thread = threading.Thread(target=self._poll, daemon=True)
@@ -81,9 +98,13 @@ class ClockSampler:
         return False
 
     def summary(self):
-        sm = [s[0] for s in self.samples]
-        mx = [s[1] for s in self.samples]
-        reasons = set().union(*[s[2] for s in self.samples]) if self.samples else set()
+        inside = self.samples
+        if self._t0 is not None:
+            t1 = self._t1 if self._t1 is not None else float("inf")
+            inside = [s for s in self.samples if self._t0 <= s[3] <= t1] or self.samples[-1:]
+        sm = [s[0] for s in inside]
+        mx = [s[1] for s in inside]
+        reasons = set().union(*[s[2] for s in inside]) if inside else set()
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self._nvml else "nvidia-smi"}
 

@@ -60,6 +60,60 @@ def test_emulated_ranks_one_gpu(world, algo):
         want = views[0][0].double().clone()
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("two_shot", [0, 1])
+def test_emulated_push_protocol_one_gpu(world, two_shot):
+    """Push (LL) all-reduce + SGD with `world` virtual ranks in one launch: tags, buffer parity, both channels, the
+    deferred weight wait, replicas bitwise identical, values against an fp64 sum."""
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    flat = 40000
+    nbytes = lib.b200cnn_comm_region_bytes(flat)
+    poff, goff = lib.b200cnn_comm_params_offset(flat), [lib.b200cnn_comm_grads_offset(flat, p) for p in (0, 1)]
+    regions = [torch.zeros(nbytes, dtype=torch.uint8, device="cuda") for _ in range(world)]
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    w0 = torch.randn(flat, device="cuda", generator=gen)
+    views = []
+    for r in range(world):
+        p = regions[r][poff:poff + 4 * flat].view(torch.float32)
+        g = [regions[r][o:o + 4 * flat].view(torch.float32) for o in goff]
+        p.copy_(w0)
+        views.append((p, g))
+    sbytes = lib.b200cnn_comm_emulate_ll_scratch_bytes(world)
+    scratch = torch.zeros(sbytes, dtype=torch.uint8, device="cuda")
+    ptrs = (C.c_void_p * world)(*[C.c_void_p(t.data_ptr()) for t in regions])
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    want = w0.double().clone()
+    for step in range(6):  # tags grow, inbox buffers alternate, slice / grid / channel change between calls
+        par = step % 2
+        grads = [torch.randn(flat, device="cuda", generator=gen) for _ in range(world)]
+        for r in range(world):
+            views[r][1][par].copy_(grads[r])
+        off, cnt = [(0, flat), (1024, 20000), (0, 4800), (36, 160), (0, flat), (8, 12000)][step]
+        blocks = [4, 2, 3, 1, 5, 2][step]
+        channel = 0 if two_shot or cnt * 4 > 128 * 1024 else step % 2
+        update = 0 if step == 3 else 1
+        N.check(lib.b200cnn_comm_emulate_ll(world, ptrs, flat, off, cnt, 0.5, two_shot, par, blocks, channel, update,
+                                            C.c_void_p(scratch.data_ptr()), st), "emulate_ll")
+        torch.cuda.synchronize()
+        assert int(scratch[sbytes - 16:sbytes - 12].view(torch.int32)[0]) == 0, "a virtual rank timed out waiting for a peer"
+        total = torch.zeros(flat, dtype=torch.float64, device="cuda")
+        for r in range(world):
+            total += grads[r].double()
+        if update:
+            want[off:off + cnt] -= (0.5 / world) * total[off:off + cnt]
+        else:  # plain all-reduce: the sum lands in every rank's gradient buffer, parameters untouched
+            for r in range(world):
+                assert torch.equal(views[r][1][par][off:off + cnt], views[0][1][par][off:off + cnt])
+            assert float((views[0][1][par][off:off + cnt].double() - total[off:off + cnt]).abs().max()) < 1e-4
+        for r in range(world):
+            assert torch.equal(views[r][0], views[0][0]), f"replica {r} differs from replica 0 after step {step}"
+        err = float((views[0][0].double() - want).abs().max())
+        assert err < 1e-5, (step, err)
+        want = views[0][0].double().clone()
+
+
 def _dp_worker(rank, world, mode, algo, steps, out_dir):
     import os
     import torch
@@ -85,17 +139,17 @@ def _dp_worker(rank, world, mode, algo, steps, out_dir):
     tr.close()
 
 
-@pytest.mark.parametrize("algo", ["auto", "one_shot", "two_shot"])
+@pytest.mark.parametrize("algo", ["auto", "one_shot", "two_shot", "ll_one_shot", "ll_two_shot", "nvls"])
 def test_multi_gpu_fused_equals_single_gpu_big_batch(algo, tmp_path):
     """W GPUs x batch B with the fused update == 1 GPU with batch W*B (same samples), replicas bitwise equal."""
-    world = min(torch.cuda.device_count(), 4)
+    world = min(torch.cuda.device_count(), 8)
     if world < 2:
         pytest.skip("needs >= 2 GPUs")
     from mpi_cuda_cnn_b200 import Engine
     from mpi_cuda_cnn_b200.ops import functional as F200
     from mpi_cuda_cnn_b200.parallel import spawn
 
-    steps, B = 3, 64
+    steps, B = 5, 64  # both step parities captured AND replayed
     spawn(_dp_worker, world, args=("fused", algo, steps, str(tmp_path)))
     reps = [np.load(tmp_path / f"fused_{algo}_{r}.npy") for r in range(world)]
     for r in range(1, world):
