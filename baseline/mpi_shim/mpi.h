@@ -13,9 +13,15 @@ typedef int MPI_Op;
 #define MPI_SUM 1
 #define MPI_IN_PLACE ((void*)1)
 #define MPI_SUCCESS 0
+#ifdef __cplusplus
+extern "C" {
+#endif
 int MPI_Init(int* argc, char*** argv);
 int MPI_Comm_rank(MPI_Comm comm, int* rank);
 int MPI_Comm_size(MPI_Comm comm, int* size);
 int MPI_Allreduce(const void* sendbuf, void* recvbuf, int count, MPI_Datatype type, MPI_Op op, MPI_Comm comm);
 int MPI_Finalize(void);
+#ifdef __cplusplus
+}
+#endif
 #endif

@@ -149,7 +149,7 @@ class _Arm:
 
         self.mode, self.world, self.device = mode, world, device
         self.use_graph = not args.no_graph
-        if world == 1 and mode == "fused":
+        if world == 1 and mode == "fused" and os.environ.get("B200CNN_BENCH_FORCE_DP") != "1":
             self.trainer = None
             self.engine = Engine(layers, max_batch=BATCH, device=device)
             self.engine.init_params(seed=0)

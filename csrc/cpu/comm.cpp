@@ -7,6 +7,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -17,12 +18,37 @@ namespace b200cnn {
 namespace {
 constexpr size_t kHeaderBytes = 256;  // keeps the slots cache-line aligned
 
+double now_seconds() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// Longest a rank waits for its peers in one barrier (B200CNN_COMM_TIMEOUT_S, default 300 s).
+double wait_limit_seconds() {
+    static const double v = [] {
+        const char* e = getenv("B200CNN_COMM_TIMEOUT_S");
+        const double d = e ? atof(e) : 0.0;
+        return d > 0 ? d : 300.0;
+    }();
+    return v;
+}
+
+// Inode of the segment `name` currently refers to (0 if it does not exist).
+ino_t named_inode(const std::string& name) {
+    const int fd = shm_open(name.c_str(), O_RDWR, 0600);
+    if (fd < 0) return 0;
+    struct stat st;
+    const ino_t ino = fstat(fd, &st) == 0 ? st.st_ino : 0;
+    close(fd);
+    return ino;
+}
+
 void init_header(void* region, int world, size_t slot_doubles) {
     ShmHeader* h = new (region) ShmHeader;
     h->arrived.store(0);
     h->sense.store(0);
     h->world = uint32_t(world);
     h->slot_doubles = slot_doubles;
+    h->failed.store(0);
+    h->joined.store(0);
+    h->go.store(0);
     h->attached.store(0x600dc0deu, std::memory_order_release);  // "initialised" marker
 }
 }  // namespace
@@ -60,16 +86,59 @@ void* ShmComm::open_named(const std::string& name, int rank, int world, size_t s
         }
         if (fd < 0) return nullptr;
     }
+    struct stat mine;
+    if (fstat(fd, &mine) != 0) mine.st_ino = 0;
     void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
     close(fd);
     if (p == MAP_FAILED) return nullptr;
+    ShmHeader* h = static_cast<ShmHeader*>(p);
+    const double t0 = now_seconds();
     if (rank == 0) {
         init_header(p, world, slot_doubles);
-    } else {
-        ShmHeader* h = static_cast<ShmHeader*>(p);
-        while (h->attached.load(std::memory_order_acquire) != 0x600dc0deu) usleep(200);
+        // Handshake: everybody must have attached to THIS segment (not to one a crashed run left behind under the
+        // same name) before anyone enters a barrier.
+        while (h->joined.load(std::memory_order_acquire) != uint32_t(world - 1)) {
+            if (now_seconds() - t0 > wait_limit_seconds()) {
+                munmap(p, bytes);
+                return nullptr;
+            }
+            usleep(200);
+        }
+        h->go.store(1, std::memory_order_release);
+        return p;
     }
-    return p;
+    // A segment whose `go` is already set before this rank has joined belongs to an earlier run (rank 0 raises it only
+    // after counting every rank of ITS run); so does one that the name no longer points to.  Drop it and look again.
+    bool stale = false;
+    while (h->attached.load(std::memory_order_acquire) != 0x600dc0deu && !stale) {
+        if (now_seconds() - t0 > 2.0 && named_inode(name) != mine.st_ino) stale = true;
+        if (now_seconds() - t0 > wait_limit_seconds()) break;
+        usleep(200);
+    }
+    if (!stale && h->attached.load(std::memory_order_acquire) == 0x600dc0deu) {
+        if (h->go.load(std::memory_order_acquire) != 0) {
+            stale = true;
+        } else {
+            h->joined.fetch_add(1, std::memory_order_acq_rel);
+            double last_check = now_seconds();
+            while (h->go.load(std::memory_order_acquire) == 0) {
+                if (now_seconds() - last_check > 1.0) {
+                    last_check = now_seconds();
+                    if (named_inode(name) != mine.st_ino) {
+                        stale = true;
+                        break;
+                    }
+                    if (last_check - t0 > wait_limit_seconds()) break;
+                }
+                usleep(200);
+            }
+            if (!stale && h->go.load(std::memory_order_acquire) != 0) return p;
+        }
+    }
+    munmap(p, bytes);
+    if (!stale || now_seconds() - t0 > wait_limit_seconds()) return nullptr;
+    usleep(20000);
+    return open_named(name, rank, world, slot_doubles);  // rank 0 of THIS run replaces the stale segment; try again
 }
 
 void ShmComm::unlink_named(const std::string& name) { shm_unlink(name.c_str()); }
@@ -88,8 +157,20 @@ void ShmComm::barrier() {
         hdr_->sense.store(local_sense_, std::memory_order_release);
     } else {
         int spins = 0;
-        while (hdr_->sense.load(std::memory_order_acquire) != local_sense_)
-            if (++spins > 64) sched_yield();  // ranks may outnumber cores (mpirun -np 8 on a laptop)
+        double t0 = 0;
+        while (hdr_->sense.load(std::memory_order_acquire) != local_sense_) {
+            if (++spins <= 64) continue;
+            sched_yield();  // ranks may outnumber cores (mpirun -np 8 on a laptop)
+            if ((spins & 1023) != 0) continue;
+            // A peer that left early (bad file, CUDA error, crash) will never arrive: stop waiting.
+            const bool peer_failed = hdr_->failed.load(std::memory_order_acquire) != 0;
+            if (t0 == 0) t0 = now_seconds();
+            if (peer_failed || now_seconds() - t0 > wait_limit_seconds()) {
+                fprintf(stderr, "rank %d: %s; leaving\n", rank_, peer_failed ? "a peer failed" : "timed out waiting for the other ranks in a barrier");
+                hdr_->failed.store(1, std::memory_order_release);
+                _exit(kCommExit);
+            }
+        }
     }
 }
 

@@ -6,7 +6,12 @@
 // transport here is a shared-memory segment between processes of one host: a sense-reversing
 // barrier, one staging slot per rank and a reduce-scatter + all-gather sum whose per-element
 // addition order is fixed by rank index (bitwise identical result on every rank, every run).
-// A real MPI backend can be compiled in with -DB200CNN_HAVE_MPI.
+// A real MPI backend (MpiComm, the same five calls) is compiled in with -DB200CNN_HAVE_MPI: `make cnnmpi_mpi`.
+//
+// Failure handling (the reference has none: a rank that returns 111 before MPI_Finalize leaves the others hanging,
+// cnnmpi.c:443): every wait inside ShmComm is bounded and watches a shared `failed` word.  A rank that gives up
+// calls abort() (or its launcher does, mark_failed()); every other rank then leaves its barrier and exits with
+// kCommExit instead of spinning forever.
 #pragma once
 #include <atomic>
 #include <cstddef>
@@ -23,7 +28,10 @@ public:
     virtual void barrier() = 0;
     virtual void allreduce_sum(double* buf, size_t n) = 0;  // in place, like MPI_IN_PLACE
     virtual void broadcast(double* buf, size_t n, int root) = 0;
+    virtual void abort() {}  // tell the peers this rank is leaving early
 };
+
+constexpr int kCommExit = 112;  // exit code of a rank whose peer failed or never arrived
 
 // Trivial single-process communicator.
 class SelfComm : public Comm {
@@ -41,6 +49,9 @@ struct ShmHeader {
     std::atomic<uint32_t> attached;
     uint32_t world;
     uint64_t slot_doubles;
+    std::atomic<uint32_t> failed;  // set by a rank (or the launcher) that gives up: barriers stop waiting
+    std::atomic<uint32_t> joined;  // named segments: non-root ranks that have attached to THIS segment
+    std::atomic<uint32_t> go;      // named segments: set by rank 0 once everybody has joined
 };
 
 class ShmComm : public Comm {
@@ -60,6 +71,9 @@ public:
     void barrier() override;
     void allreduce_sum(double* buf, size_t n) override;
     void broadcast(double* buf, size_t n, int root) override;
+    void abort() override { hdr_->failed.store(1, std::memory_order_release); }
+    // For a launcher that holds the mapping but is not a rank: release everybody who is waiting.
+    static void mark_failed(void* region) { static_cast<ShmHeader*>(region)->failed.store(1, std::memory_order_release); }
 
 private:
     double* slot(int r) const { return slots_ + size_t(r) * slot_doubles_; }

@@ -106,6 +106,13 @@ int load_data(const TrainOptions& opt, DataSet& data) {
         fprintf(stderr, "image / label files do not match\n");
         return kFileError;
     }
+    // The network reads item_size() bytes per image: a smaller or larger image file would make set_inputs read past
+    // the sample (the reference memcpy's a fixed 28*28, cnn.c:399-402, and checks nothing).
+    if (data.train_y.dims.size() != 1 || data.test_y.dims.size() != 1 || data.train_x.item_size() != 28 * 28 ||
+        data.test_x.item_size() != 28 * 28) {
+        fprintf(stderr, "expected 28x28 images (idx3) and 1-D label files (idx1)\n");
+        return kFileError;
+    }
     return kOk;
 }
 
@@ -270,7 +277,15 @@ int run_data_parallel(const TrainOptions& opt, Comm& comm) {
     comm.allreduce_sum(&status, 1);
     if (status != 0) return rc ? rc : kFileError;
     std::string err;
-    if (!opt.load_path.empty() && rank == 0 && !net.load(opt.load_path, &err)) fprintf(stderr, "%s\n", err.c_str());
+    // Same agreement for the checkpoint: a failed --load on rank 0 ends the run on every rank (run_serial returns
+    // kFileError too) instead of silently training from the random initialisation.
+    status = 0;
+    if (!opt.load_path.empty() && rank == 0 && !net.load(opt.load_path, &err)) {
+        fprintf(stderr, "%s\n", err.c_str());
+        status = 1;
+    }
+    comm.allreduce_sum(&status, 1);
+    if (status != 0) return kFileError;
 
     std::vector<double> flat;
     net.gather_params(flat);

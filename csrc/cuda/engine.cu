@@ -134,6 +134,19 @@ bool use_head(const b200cnn_engine* e, int batch) {
     return tc_head_supported(batch, L[n - 3].nnodes, L[n - 2].nnodes, L[n - 1].nnodes, L[n - 1].ld);
 }
 
+// True when the last three layers are FC(tanh) -> FC(tanh) -> FC(softmax) on top of a float layer and the cluster
+// kernel of tc_chain.cu takes the shape: forward of the three layers, loss gradient and the three data gradients then
+// run as ONE launch.
+bool use_chain(const b200cnn_engine* e, int batch) {
+    const auto& L = e->layers;
+    const size_t n = L.size();
+    if (n < 5 || !tc_fc_chain_enabled()) return false;
+    for (size_t i = n - 3; i < n; i++)
+        if (L[i].d.type != B200CNN_LAYER_FULL) return false;
+    if (L[n - 4].d.type == B200CNN_LAYER_INPUT || L[n - 4].ld != L[n - 4].nnodes) return false;
+    return tc_fc_chain_supported(batch, L[n - 4].nnodes, L[n - 3].nnodes, L[n - 2].nnodes, L[n - 1].nnodes, L[n - 1].ld);
+}
+
 // Forward through layers [1, stop).
 int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
                     cudaStream_t st, int* launches, size_t stop = ~size_t(0)) {
@@ -238,8 +251,9 @@ static bool fused_tail_requested() {
     return on;
 }
 
+// dx_done: the data gradients INTO the last `dx_done` layers' inputs already exist (fused head / chain kernel).
 int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch, cudaStream_t st, int* launches,
-                     bool head_done = false, bool fuse_update = false) {
+                     int dx_done = 0, bool fuse_update = false) {
     auto& L = e->layers;
     float* grads = cur_grads(e);
     const bool fast = use_fast_chain(e);
@@ -313,7 +327,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
 
         // Data gradient for the layer below (critical path); the fused head kernel has already produced it for
         // the last two layers.
-        if (li > 1 && !(head_done && li + 2 >= L.size())) {
+        if (li > 1 && li + size_t(dx_done) < L.size()) {
             if (l.d.type == B200CNN_LAYER_FULL) {
                 rc = b200cnn_linear_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, batch, l.nnodes, p.nnodes, l.ld, st);
             } else {
@@ -648,10 +662,25 @@ extern "C" int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream st
 
 static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
                         cudaStream_t st, int* launches, bool update = true) {
-    const bool head = use_head(e, batch);
+    const bool chain = use_chain(e, batch);
+    const bool head = !chain && use_head(e, batch);
     if (e->comm)
         if (int rc = comm_begin_step(e->comm, st)) return rc;
-    if (!head) {
+    if (chain) {
+        // layers below the fully connected part, then ONE cluster kernel for fc -> fc -> softmax/loss and all three
+        // data-gradient GEMMs (tc_chain.cu)
+        auto& L = e->layers;
+        const size_t n = L.size();
+        if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches, n - 3)) return rc;
+        if (e->comm)
+            if (int rc = comm_weights_ready(e->comm, st)) return rc;
+        EngineLayer &l0 = L[n - 4], &l1 = L[n - 3], &l2 = L[n - 2], &l3 = L[n - 1];
+        if (int rc = tc_fc_chain(l0.a, l0.act, e->params + l1.w_off, e->params + l1.b_off, e->params + l2.w_off, e->params + l2.b_off,
+                                 e->params + l3.w_off, e->params + l3.b_off, labels, l1.a, l2.a, l3.a, l3.dz, l2.dz, l1.dz, l0.dz,
+                                 e->metrics, batch, l0.nnodes, l1.nnodes, l2.nnodes, l3.nnodes, l3.ld, st))
+            return rc;
+        if (launches) (*launches)++;
+    } else if (!head) {
         if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches)) return rc;
     } else {
         // layers below the head, then ONE kernel for fc -> softmax/loss -> both backward-data GEMMs
@@ -665,7 +694,7 @@ static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const 
         if (launches) (*launches)++;
     }
     const bool fuse = update && can_fuse_update(e);
-    if (int rc = enqueue_backward(e, images, is_u8, batch, st, launches, head, fuse)) return rc;
+    if (int rc = enqueue_backward(e, images, is_u8, batch, st, launches, chain ? 3 : head ? 2 : 0, fuse)) return rc;
     return (update && !fuse) ? enqueue_update(e, st, launches) : 0;
 }
 

@@ -127,6 +127,17 @@ int b200cnn_mlp_head(const float* h1, const float* w2, const float* b2, const fl
                      float* h2, float* probs, float* dz3, float* dz2, float* dz1, float* metrics, int m, int n1, int n2, int nc,
                      int ldc, b200cnn_stream stream);
 
+/* The whole fully connected part of a training step in ONE cluster kernel (csrc/cuda/tc_chain.cu):
+ *   h1 = tanh(x W1^T + b1); h2 = tanh(h1 W2^T + b2); probs = softmax(h2 W3^T + b3); dz3 = probs - onehot, metrics;
+ *   dz2 = (dz3 W3) * (1 - h2^2); dz1 = (dz2 W2) * (1 - h1^2); dx = (dz1 W1) * act_x'(x).
+ * x [m][k1] (k1 % 4 == 0, 32 <= k1 <= 2048), w1 [n1][k1], w2 [n2][n1], w3 [nc][n2]; 8 <= n1, n2 <= 224 (multiples of 4),
+ * nc <= ldc <= 16.  Replaces Layer_feedForw_full x3 (cnn.c:113-152), the loss gradient + metric (cnn.c:275-286) and
+ * the error-propagation half of Layer_feedBack_full x3 (cnn.c:158-166) for a whole mini-batch. */
+int b200cnn_fc_chain(const float* x, int act_x, const float* w1, const float* b1, const float* w2, const float* b2,
+                     const float* w3, const float* b3, const uint8_t* labels, float* h1, float* h2, float* probs, float* dz3,
+                     float* dz2, float* dz1, float* dx, float* metrics, int m, int k1, int n1, int n2, int nc, int ldc,
+                     b200cnn_stream stream);
+
 /* ---- max pooling (K7; not in the reference) ------------------------------------------------ */
 int b200cnn_maxpool_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride,
                         b200cnn_stream stream);

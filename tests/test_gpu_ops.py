@@ -251,6 +251,57 @@ def test_fused_head_kernel(shape):
     assert got[0] == pytest.approx(float(-torch.log(rp[torch.arange(m), lab.long()]).sum()), rel=2e-3)
 
 
+@pytest.mark.parametrize("shape", [(256, 1568, 200, 200, 10), (16, 1568, 200, 200, 10), (37, 1568, 200, 200, 10),
+                                   (5, 64, 40, 24, 3), (130, 800, 208, 120, 16), (64, 196, 200, 200, 10)])
+@pytest.mark.parametrize("act_x", ["relu", "none"])
+def test_fc_chain_kernel(shape, act_x):
+    """tc_chain.cu: three FC layers forward, softmax + loss gradient + metrics and the three data-gradient GEMMs in
+    one 8-CTA-cluster kernel, against plain PyTorch fp32 (TF32 off), twice in a row (barriers / TMEM are per launch)."""
+    import ctypes as C
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    m, k1, n1, n2, nc = shape
+    torch.backends.cuda.matmul.allow_tf32 = False
+    x = torch.randn(m, k1, device="cuda")
+    if act_x == "relu":
+        x = torch.relu(x)
+    w1, b1 = torch.randn(n1, k1, device="cuda") / k1 ** 0.5, 0.1 * torch.randn(n1, device="cuda")
+    w2, b2 = torch.randn(n2, n1, device="cuda") / n1 ** 0.5, 0.1 * torch.randn(n2, device="cuda")
+    w3, b3 = torch.randn(nc, n2, device="cuda") / n2 ** 0.5, 0.1 * torch.randn(nc, device="cuda")
+    lab = torch.randint(0, nc, (m,), device="cuda", dtype=torch.uint8)
+    rh1 = torch.tanh(x @ w1.T + b1)
+    rh2 = torch.tanh(rh1 @ w2.T + b2)
+    rp = torch.softmax(rh2 @ w3.T + b3, 1)
+    rdz3 = rp - F.one_hot(lab.long(), nc)
+    rdz2 = (rdz3 @ w3) * (1 - rh2 ** 2)
+    rdz1 = (rdz2 @ w2) * (1 - rh1 ** 2)
+    rdx = rdz1 @ w1
+    if act_x == "relu":
+        rdx = rdx * (x > 0)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for rep in range(2):
+        h1, dz1 = torch.full((m, n1), 9.0, device="cuda"), torch.full((m, n1), 9.0, device="cuda")
+        h2, dz2 = torch.full((m, n2), 9.0, device="cuda"), torch.full((m, n2), 9.0, device="cuda")
+        pr, dz3 = torch.full((m, 16), 9.0, device="cuda"), torch.full((m, 16), 9.0, device="cuda")
+        dx, met = torch.full((m, k1), 9.0, device="cuda"), torch.zeros(4, device="cuda")
+        N.check(lib.b200cnn_fc_chain(p(x), N.ACT_RELU if act_x == "relu" else N.ACT_NONE, p(w1), p(b1), p(w2), p(b2), p(w3), p(b3), p(lab),
+                                     p(h1), p(h2), p(pr), p(dz3), p(dz2), p(dz1), p(dx), p(met), m, k1, n1, n2, nc, 16, st), "fc_chain")
+        torch.cuda.synchronize()
+        for name, got, want in (("h1", h1, rh1), ("h2", h2, rh2), ("probs", pr[:, :nc], rp), ("dz3", dz3[:, :nc], rdz3),
+                                ("dz2", dz2, rdz2), ("dz1", dz1, rdz1), ("dx", dx, rdx)):
+            err = float((got - want).abs().max() / want.abs().max().clamp_min(1e-6))
+            assert err < 6e-3, (name, rep, err)
+        if nc < 16:
+            assert float(pr[:, nc:].abs().max()) == 0.0 and float(dz3[:, nc:].abs().max()) == 0.0
+        got = met.cpu().numpy()
+        assert got[3] == m
+        assert abs(got[2] - float((rp.argmax(1) == lab.long()).sum())) <= 1  # a TF32 near-tie may flip one argmax
+        assert got[0] == pytest.approx(float(-torch.log(rp[torch.arange(m), lab.long()]).sum()), rel=3e-3)
+        assert got[1] == pytest.approx(float((rdz3 ** 2).sum() / nc), rel=3e-3)
+
+
 @pytest.mark.parametrize("n", [8, 72, 256, 20])
 @pytest.mark.parametrize("backend", ["simt", "auto"])
 def test_nhwc_conv2_weight_gradient(n, backend):

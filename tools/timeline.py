@@ -16,9 +16,25 @@ from mpi_cuda_cnn_b200.ops import functional as F200
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 STEPS = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+WORLD = int(os.environ.get("WORLD_SIZE", "1"))
+RANK = int(os.environ.get("RANK", "0"))
 dev = torch.device("cuda:0")
-eng = Engine(max_batch=B, device=dev)
-eng.init_params(seed=1)
+if WORLD > 1:  # under torchrun: every rank trains, every rank prints its own view (timeline_dp: rank 0 and the last rank matter)
+    from mpi_cuda_cnn_b200.parallel import DataParallelTrainer, init_distributed
+    RANK, WORLD, dev = init_distributed()
+    _tr = DataParallelTrainer(RANK, WORLD, dev, batch=B, mode="fused")
+    eng = _tr.engine
+    if RANK not in (0, WORLD - 1):
+        sys.stdout = open(os.devnull, "w")
+    else:
+        sys.stdout = open(os.environ.get("TIMELINE_OUT", "timeline") + f".rank{RANK}.txt", "w")
+elif os.environ.get("B200CNN_BENCH_FORCE_DP") == "1":  # the data-parallel launch structure with a world of one
+    from mpi_cuda_cnn_b200.parallel import DataParallelTrainer
+    _tr = DataParallelTrainer(0, 1, dev, batch=B, mode="fused")
+    eng = _tr.engine
+else:
+    eng = Engine(max_batch=B, device=dev)
+    eng.init_params(seed=1)
 x, y = F200.synthetic_batch(B * 8, seed=1, device=dev)
 xs = [x[i * B:(i + 1) * B].contiguous() for i in range(8)]
 ys = [y[i * B:(i + 1) * B].contiguous() for i in range(8)]
@@ -50,3 +66,8 @@ for e in step:
     print(f"{s:8.2f} {d:7.2f} {gap:7.2f}  {sid!s:>6}  {e.name[:90]}")
 nxt = ev[k0 + per].time_range.start - t0 if k0 + per < len(ev) else float("nan")
 print(f"next step starts at {nxt:.2f} us; busy (sum of durations) {sum(e.time_range.end - e.time_range.start for e in step):.2f} us")
+sys.stdout.flush()
+if WORLD > 1:
+    import torch.distributed as dist
+    dist.barrier()
+    dist.destroy_process_group()
