@@ -56,6 +56,8 @@ def link_bytes(path, nbytes, world, multicast):
     if algo == "auto":  # what AUTO resolves to (include/b200cnn_comm.h)
         if nbytes * (w - 1) <= (448 << 10):
             algo = "ll_one_shot"
+        elif multicast and w >= 4 and nbytes >= (256 << 10):
+            algo = "nvls"
         elif nbytes // w + 32 <= (1 << 20) and nbytes <= (8 << 20):
             algo = "ll_two_shot"
         else:

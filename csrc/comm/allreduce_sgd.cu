@@ -336,68 +336,135 @@ ll_allreduce_kernel(CommView v, size_t off4, size_t n4, const float* __restrict_
     const size_t tid = size_t(blockIdx.x) * blockDim.x + threadIdx.x, nthreads = size_t(gridDim.x) * blockDim.x;
     bool ok = true;
 
-    if (!two_shot) {
-        for (size_t i = tid; i < n4; i += nthreads) {
-            const float4 mine = g_local[i];
+    // Every loop below first puts all of an iteration's loads in flight (its own gradients / weights and a first look
+    // at every peer's packets) and only then consumes them: the kernel moves a few hundred KB per rank and was bound
+    // by one dependent memory latency per element before (22 us for 1.4 MB at 2 ranks).
+    constexpr int WW = W > 0 ? W : kMaxRanks;
+    constexpr int U = Unroll<W>::value;  // elements per thread per trip: U x (W-1) packets in flight
+    auto reduce_batch = [&](size_t i, size_t stride, size_t end, size_t slot_base, float4 (&acc)[U]) {
+        uint4 pa[U][WW], pb[U][WW];
+        float4 own[U];
 #pragma unroll
-            for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++)
-                if (k < world && k != rank) ll::push4(ll::slot_ptr(c, k, buf, rank), i, mine, tag);
+        for (int u = 0; u < U; u++) {
+            const size_t idx = i + size_t(u) * stride;
+            if (idx >= end) continue;
+            own[u] = g_local[idx];
+#pragma unroll
+            for (int k = 0; k < WW; k++)
+                if (k < world && k != rank) {
+                    const uint4* slot = ll::slot_ptr(c, rank, buf, k);
+                    pa[u][k] = ll::ld_packet(slot + 2 * (idx - slot_base));
+                    pb[u][k] = ll::ld_packet(slot + 2 * (idx - slot_base) + 1);
+                }
         }
-        for (size_t i = tid; i < n4 && ok; i += nthreads) {
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++) {
+        for (int u = 0; u < U; u++) {
+            const size_t idx = i + size_t(u) * stride;
+            if (idx >= end) continue;
+            float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int k = 0; k < WW; k++) {
                 if (k >= world) continue;
-                float4 t4;
-                if (k == rank) t4 = g_local[i];
-                else ok = ok && ll::poll4(ll::slot_ptr(c, rank, buf, k), i, tag, t4);
-                acc = k == 0 ? t4 : add4(acc, t4);
+                float4 t4 = own[u];
+                if (k != rank) {
+                    const uint4 x = pa[u][k], y = pb[u][k];
+                    if (x.y == tag && x.w == tag && y.y == tag && y.w == tag)
+                        t4 = make_float4(__uint_as_float(x.x), __uint_as_float(x.z), __uint_as_float(y.x), __uint_as_float(y.z));
+                    else
+                        ok = ok && ll::poll4(ll::slot_ptr(c, rank, buf, k), idx - slot_base, tag, t4);  // not there yet: spin
+                }
+                sum = k == 0 ? t4 : add4(sum, t4);  // rank order: bitwise identical on every rank
             }
-            if (!ok) break;
+            acc[u] = sum;
+        }
+    };
+
+    if (!two_shot) {
+        for (size_t i = tid; i < n4; i += nthreads * 4) {
+            float4 mine[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                if (i + u * nthreads < n4) mine[u] = g_local[i + u * nthreads];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (i + u * nthreads >= n4) continue;
+#pragma unroll
+                for (int k = 0; k < WW; k++)
+                    if (k < world && k != rank) ll::push4(ll::slot_ptr(c, k, buf, rank), i + u * nthreads, mine[u], tag);
+            }
+        }
+        for (size_t i = tid; i < n4 && ok; i += nthreads * U) {
+            float4 acc[U], w[U];
             if (op == kOpSgd) {
-                float4 w = w_local[i];
-                w.x -= lr * acc.x;
-                w.y -= lr * acc.y;
-                w.z -= lr * acc.z;
-                w.w -= lr * acc.w;
-                w_local[i] = w;
-            } else {
-                g_local[i] = acc;
+#pragma unroll
+                for (int u = 0; u < U; u++)
+                    if (i + u * nthreads < n4) w[u] = w_local[i + u * nthreads];
+            }
+            reduce_batch(i, nthreads, n4, 0, acc);
+            if (!ok) break;
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const size_t idx = i + u * nthreads;
+                if (idx >= n4) continue;
+                if (op == kOpSgd) {
+                    w[u].x -= lr * acc[u].x;
+                    w[u].y -= lr * acc[u].y;
+                    w[u].z -= lr * acc[u].z;
+                    w[u].w -= lr * acc[u].w;
+                    w_local[idx] = w[u];
+                } else {
+                    g_local[idx] = acc[u];
+                }
             }
         }
     } else {
-        // reduce-scatter: my part of shard s goes to rank s
+        // reduce-scatter: my part of shard s goes to rank s; one element of every peer's shard per trip
+        size_t longest = 0;
 #pragma unroll
-        for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++) {
-            if (k >= world || k == rank) continue;
-            const size_t lo = n4 * size_t(k) / world, hi = n4 * size_t(k + 1) / world;
-            uint4* slot = ll::slot_ptr(c, k, buf, rank);
-            for (size_t i = lo + tid; i < hi; i += nthreads) ll::push4(slot, i - lo, g_local[i], tag);
+        for (int k = 0; k < WW; k++)
+            if (k < world) longest = max(longest, n4 * size_t(k + 1) / world - n4 * size_t(k) / world);
+        for (size_t base = tid; base < longest; base += nthreads) {
+            float4 mine[WW];
+#pragma unroll
+            for (int k = 0; k < WW; k++) {
+                if (k >= world || k == rank) continue;
+                const size_t lo = n4 * size_t(k) / world, hi = n4 * size_t(k + 1) / world;
+                if (lo + base < hi) mine[k] = g_local[lo + base];
+            }
+#pragma unroll
+            for (int k = 0; k < WW; k++) {
+                if (k >= world || k == rank) continue;
+                const size_t lo = n4 * size_t(k) / world, hi = n4 * size_t(k + 1) / world;
+                if (lo + base < hi) ll::push4(ll::slot_ptr(c, k, buf, rank), base, mine[k], tag);
+            }
         }
         const size_t lo = n4 * size_t(rank) / world, hi = n4 * size_t(rank + 1) / world;
         const size_t dst_off = (op == kOpSgd) ? v.params_off : v.grads_off[parity];
-        for (size_t i = lo + tid; i < hi && ok; i += nthreads) {
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++) {
-                if (k >= world) continue;
-                float4 t4;
-                if (k == rank) t4 = g_local[i];
-                else ok = ok && ll::poll4(ll::slot_ptr(c, rank, buf, k), i - lo, tag, t4);
-                acc = k == 0 ? t4 : add4(acc, t4);
-            }
-            if (!ok) break;
-            float4 out = acc;
+        for (size_t i = lo + tid; i < hi && ok; i += nthreads * U) {
+            float4 acc[U], out[U];
             if (op == kOpSgd) {
-                out = w_local[i];
-                out.x -= lr * acc.x;
-                out.y -= lr * acc.y;
-                out.z -= lr * acc.z;
-                out.w -= lr * acc.w;
-            }
 #pragma unroll
-            for (int k = 0; k < (W > 0 ? W : kMaxRanks); k++)
-                if (k < world) st_peer(reinterpret_cast<float4*>(v.region[k] + dst_off) + off4 + i, out);
+                for (int u = 0; u < U; u++)
+                    if (i + u * nthreads < hi) out[u] = w_local[i + u * nthreads];
+            }
+            reduce_batch(i, nthreads, hi, lo, acc);
+            if (!ok) break;
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const size_t idx = i + u * nthreads;
+                if (idx >= hi) continue;
+                if (op == kOpSgd) {
+                    out[u].x -= lr * acc[u].x;
+                    out[u].y -= lr * acc[u].y;
+                    out[u].z -= lr * acc[u].z;
+                    out[u].w -= lr * acc[u].w;
+                } else {
+                    out[u] = acc[u];
+                }
+#pragma unroll
+                for (int k = 0; k < WW; k++)
+                    if (k < world) st_peer(reinterpret_cast<float4*>(v.region[k] + dst_off) + off4 + idx, out[u]);
+            }
         }
     }
     if (!ok) atomicExch(v.errflag, 1u);
@@ -488,8 +555,12 @@ int resolve_algo(const b200cnn_comm* c, int algo, size_t count, int op, int ch) 
     if (algo == B200CNN_ALGO_AUTO && ll_enabled()) {
         // Push protocol wherever the slice fits an inbox: one-shot while every rank can afford to send the whole
         // slice to everybody ((W-1) x 2 x bytes over its links), two-shot while a shard fits a slot.
+        // Measured (profiles/allreduce_sweep_w8.json, 8 ranks): push one-shot 9.4 / 12.6 us at 4 / 64 KB against 11.0 /
+        // 23.0 for the pull kernel; from 256 KB the switch reduction wins where the box has it (NVLS 16.5 / 20.0 us at
+        // 256 KB / 1.44 MB against 19.6 / 28.0 for push two-shot), so push two-shot is the choice only without multicast.
         const size_t bytes = count * sizeof(float);
         if (bytes <= payload && bytes * size_t(c->view.world - 1) <= (448u << 10)) return B200CNN_ALGO_LL_ONE_SHOT;
+        if (c->view.mc_region && c->view.world >= 4 && bytes >= (256u << 10)) return B200CNN_ALGO_NVLS;
         if (shard <= payload && bytes <= (8u << 20)) return B200CNN_ALGO_LL_TWO_SHOT;
     }
     if (algo == B200CNN_ALGO_LL_ONE_SHOT && count * sizeof(float) > payload) algo = B200CNN_ALGO_LL_TWO_SHOT;
@@ -749,7 +820,7 @@ int comm_allreduce_sgd_slice(b200cnn_comm* c, size_t offset, size_t count, const
     // Few blocks: the kernel shares the GPU with the rest of backward.  (B200CNN_COMM_BLOCKS overrides, <= 64.)
     static const int max_blocks = [] {
         const char* s = std::getenv("B200CNN_COMM_BLOCKS");
-        const int v = s ? std::atoi(s) : 16;
+        const int v = s ? std::atoi(s) : 32;
         return v < 1 ? 1 : v > kMaxBlocks / 2 ? kMaxBlocks / 2 : v;
     }();
     return enqueue(c, offset, count, lr_dev, 0.0f, B200CNN_ALGO_AUTO, c->parity, kOpSgd, 0, max_blocks, c->stream, 0, 4, /*ch=*/0,

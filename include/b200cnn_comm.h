@@ -67,9 +67,9 @@ int b200cnn_comm_world(const b200cnn_comm* c);
 int b200cnn_comm_has_multicast(const b200cnn_comm* c);
 float* b200cnn_comm_params(b200cnn_comm* c);
 float* b200cnn_comm_grads(b200cnn_comm* c, int parity);
-/* Algorithm used by the engine's bucket launches.  AUTO: push one-shot while (world-1) x bytes <= 448 KiB, push
- * two-shot while a 1/world shard fits an inbox slot (1 MiB) and the slice is <= 8 MiB; beyond that the pull kernels by
- * measured crossover (NVLS from 8 MiB when a multicast mapping exists, else two-shot).  B200CNN_LL=0 in the
+/* Algorithm used by the engine's bucket launches.  AUTO: push one-shot while (world-1) x bytes <= 448 KiB; NVLS from
+ * 256 KiB when a multicast mapping exists and world >= 4; else push two-shot while a 1/world shard fits an inbox slot
+ * (1 MiB) and the slice is <= 8 MiB; beyond that the pull kernels (two-shot, or NVLS from 8 MiB).  B200CNN_LL=0 in the
  * environment removes the push algorithms from AUTO. */
 int b200cnn_comm_set_algo(b200cnn_comm* c, int algo);
 /* 0 if no kernel of this communicator ever timed out waiting for a peer; the kernels give up after
