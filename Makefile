@@ -80,12 +80,12 @@ $(LIBDIR)/libb200cnn_cuda.so: $(CUDA_OBJS)
 	@mkdir -p $(LIBDIR)
 	$(NVCC) $(SM_ARCH) -shared -o $@ $^ -lcudart
 
-$(BINDIR)/cudacnn: csrc/apps/cudacnn_main.cpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o
+$(BINDIR)/cudacnn: csrc/apps/cudacnn_main.cpp csrc/apps/gpu_app_common.hpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o
 	@mkdir -p $(BINDIR)
 	$(CXX) $(CXXFLAGS) -Iinclude -I/usr/local/cuda/include -o $@ csrc/apps/cudacnn_main.cpp $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o \
 	    -L$(LIBDIR) -lb200cnn_cuda -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$$ORIGIN/../$(LIBDIR)'
 
-$(BINDIR)/cudampi: csrc/apps/cudampi_main.cpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o $(OBJDIR)/cpu/comm.o
+$(BINDIR)/cudampi: csrc/apps/cudampi_main.cpp csrc/apps/gpu_app_common.hpp csrc/cpu/comm.hpp $(LIBDIR)/libb200cnn_cuda.so $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o $(OBJDIR)/cpu/comm.o
 	@mkdir -p $(BINDIR)
 	$(CXX) $(CXXFLAGS) -Iinclude -I/usr/local/cuda/include -o $@ csrc/apps/cudampi_main.cpp $(OBJDIR)/cpu/idx.o $(OBJDIR)/cpu/net.o $(OBJDIR)/cpu/comm.o \
 	    -L$(LIBDIR) -lb200cnn_cuda -L/usr/local/cuda/lib64 -lcudart -lrt -Wl,-rpath,'$$ORIGIN/../$(LIBDIR)'

@@ -3,20 +3,14 @@
 // device as uint8, every step gathers a random mini-batch on the device (cnn.c:455 samples with
 // replacement) and replays the engine's CUDA graph.
 //
-//   cudacnn [--rate 0.1 --nepoch 10 --batch-size 256 --seed 0 --log-every 1000 --synthetic N --timing]
+//   cudacnn [--rate 0.1 --nepoch 10 --batch-size 256 --seed 0 --log-every 1000 --synthetic N --synthetic-test N
+//            --pool --backend auto|simt|tcgen05 --save F --load F --timing]
 //           train-images train-labels test-images test-labels
 #include <cuda_runtime.h>
 
 #include <chrono>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <string>
-#include <vector>
 
-#include "../cpu/idx.hpp"
-#include "../cpu/net.hpp"
-#include "b200cnn.h"
+#include "gpu_app_common.hpp"
 
 using namespace b200cnn;
 
@@ -38,61 +32,25 @@ using namespace b200cnn;
     } while (0)
 
 int main(int argc, char** argv) {
-    double rate = 0.1;
-    int nepoch = 10, batch = 256, log_every = 1000, synthetic = 0;
-    unsigned seed = 0;
-    bool timing = false;
-    std::vector<std::string> pos;
-    for (int i = 1; i < argc; i++) {
-        const std::string a = argv[i];
-        auto val = [&]() -> const char* { return i + 1 < argc ? argv[++i] : nullptr; };
-        const char* v = nullptr;
-        if (a == "--rate") { if (!(v = val())) return 100; rate = atof(v); }
-        else if (a == "--nepoch") { if (!(v = val())) return 100; nepoch = atoi(v); }
-        else if (a == "--batch-size") { if (!(v = val())) return 100; batch = atoi(v); }
-        else if (a == "--seed") { if (!(v = val())) return 100; seed = unsigned(strtoul(v, nullptr, 10)); }
-        else if (a == "--log-every") { if (!(v = val())) return 100; log_every = atoi(v); }
-        else if (a == "--synthetic") { if (!(v = val())) return 100; synthetic = atoi(v); }
-        else if (a == "--timing") timing = true;
-        else if (a.rfind("--", 0) == 0) { fprintf(stderr, "unknown option %s\n", a.c_str()); return 100; }
-        else pos.push_back(a);
-    }
-    if (synthetic <= 0 && pos.size() < 4) return 100;  // cnn.c:412
-    if (batch < 1 || nepoch < 0) return 100;
-
+    app::Options o;
+    if (int rc = app::parse(argc, argv, /*dp=*/false, o)) return rc;
     IdxFile tx, ty, ex, ey;
-    if (synthetic > 0 && pos.size() < 4) {
-        make_synthetic(uint32_t(synthetic), 28, 28, 10, 1, tx, ty);
-        make_synthetic(uint32_t(std::max(100, synthetic / 5)), 28, 28, 10, 2, ex, ey);
-    } else {
-        std::string err;
-        IdxFile* f[4] = {&tx, &ty, &ex, &ey};
-        for (int i = 0; i < 4; i++)
-            if (!idx_read(pos[i], *f[i], &err)) {
-                fprintf(stderr, "%s\n", err.c_str());
-                return 111;  // cnn.c:432-442
-            }
-    }
+    if (int rc = app::load_data(o, tx, ty, ex, ey)) return rc;
 
-    // Reference topology and initialisation (cnn.c:413-428) through the CPU engine's generator.
-    GlibcRand rng(seed);
-    Net cpu = Net::mnist(rng);
-    std::vector<double> p64;
-    cpu.gather_params(p64);
-    std::vector<float> p32(p64.begin(), p64.end());
-    const b200cnn_layer_desc layers[6] = {{B200CNN_LAYER_INPUT, 1, 28, 28, 0, 0, 1},   {B200CNN_LAYER_CONV, 16, 14, 14, 3, 1, 2},
-                                          {B200CNN_LAYER_CONV, 32, 7, 7, 3, 1, 2},     {B200CNN_LAYER_FULL, 200, 1, 1, 0, 0, 1},
-                                          {B200CNN_LAYER_FULL, 200, 1, 1, 0, 0, 1},    {B200CNN_LAYER_FULL, 10, 1, 1, 0, 0, 1}};
     CU(cudaSetDevice(0));
-    b200cnn_engine* eng = b200cnn_engine_create(layers, 6, batch);
+    CK(b200cnn_set_backend(o.backend));
+    const std::vector<b200cnn_layer_desc> layers = app::topology(o.pool);
+    b200cnn_engine* eng = b200cnn_engine_create(layers.data(), int(layers.size()), o.batch);
     if (!eng) {
         fprintf(stderr, "engine_create: %s\n", b200cnn_last_error());
         return 1;
     }
+    std::vector<float> p32;
+    if (int rc = app::initial_params(o, b200cnn_engine_num_params(eng), p32)) return rc;
     CK(b200cnn_engine_set_params(eng, p32.data()));
 
     const uint32_t train_size = tx.count(), ntests = ex.count();
-    const int item = int(tx.item_size());
+    const int item = int(tx.item_size()), batch = o.batch;
     uint8_t *d_tx, *d_ty, *d_ex, *d_ey, *xs, *ys;
     CU(cudaMalloc(&d_tx, tx.data.size()));
     CU(cudaMalloc(&d_ty, ty.data.size()));
@@ -110,24 +68,28 @@ int main(int argc, char** argv) {
     fprintf(stderr, "training...\n");
     float metrics[4];
     CK(b200cnn_engine_reset_metrics(eng, st));
-    const long steps = long(nepoch) * std::max<long>(train_size / batch, 1);
+    const long steps = long(o.nepoch) * std::max<long>(train_size / batch, 1);
     long seen = 0, next_log = 0;
     const auto t0 = std::chrono::steady_clock::now();
     for (long step = 0; step < steps; step++) {
-        CK(b200cnn_gather_batch(d_tx, d_ty, train_size, item, xs, ys, batch, seed + 1, uint64_t(step), 0, train_size, st));
-        CK(b200cnn_engine_train_step(eng, xs, 1, ys, batch, float(rate / batch), 1, st));
+        CK(b200cnn_gather_batch(d_tx, d_ty, train_size, item, xs, ys, batch, o.seed + 1, uint64_t(step), 0, train_size, st));
+        CK(b200cnn_engine_train_step(eng, xs, 1, ys, batch, float(o.rate / batch), 1, st));
         seen += batch;
         if (seen > next_log) {
             CU(cudaMemcpyAsync(metrics, b200cnn_engine_metrics(eng), sizeof(metrics), cudaMemcpyDeviceToHost, st));
             CU(cudaStreamSynchronize(st));
             CK(b200cnn_engine_reset_metrics(eng, st));
             if (metrics[3] > 0) fprintf(stderr, "i=%ld, error=%.4f\n", seen - batch, metrics[1] / metrics[3]);
-            next_log += std::max(log_every, batch);
+            next_log += std::max(o.log_every, batch);
         }
     }
     CU(cudaStreamSynchronize(st));
     const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    if (timing && steps) fprintf(stderr, "train_images_per_sec=%.1f (%ld samples in %.3f s)\n", steps * batch / dt, steps * batch, dt);
+    if (o.timing && steps) fprintf(stderr, "train_images_per_sec=%.1f (%ld samples in %.3f s)\n", steps * batch / dt, steps * batch, dt);
+    if (!o.save_path.empty()) {
+        CK(b200cnn_engine_get_params(eng, p32.data()));
+        if (int rc = app::save_params(o.save_path, p32)) return rc;
+    }
 
     fprintf(stderr, "testing...\n");
     long ncorrect = 0;

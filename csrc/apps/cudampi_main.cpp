@@ -2,52 +2,46 @@
 // needed mpirun + MPI_Init and never selected a GPU).  One process per GPU, forked by this launcher:
 //   * rank r owns GPU r; its parameter / gradient region is cudaMalloc'd and shared with the peers through
 //     64-byte CUDA IPC handles exchanged over an anonymous shared mapping (no MPI, no NCCL, no Python);
-//   * the fused all-reduce + 1/world + SGD kernels of libb200cnn_cuda read the peers' gradients over NVLink;
-//   * data is sharded contiguously by rank (cnnmpi.c:456-458), rank 0 evaluates (cnnmpi.c:521).
+//   * the fused all-reduce + 1/world + SGD kernels of libb200cnn_cuda move gradients over NVLink (push protocol for
+//     small slices, two-shot for the big bucket).  CUDA IPC memory has no multicast mapping, so the in-switch (NVLS)
+//     variant is only reachable through the Python launcher, which allocates symmetric memory;
+//   * data is sharded contiguously by rank (cnnmpi.c:456-458), rank 0 evaluates (cnnmpi.c:521);
+//   * a rank that fails (bad file, CUDA error, too few GPUs) marks the shared rendezvous area, so its peers leave
+//     their barriers with exit code 112 instead of spinning, and the launcher reports the first failure.
 //
-//   cudampi -np N [--rate 0.1 --nepoch 10 --batch-size 256 --seed 0 --log-every 1000 --synthetic M --timing
-//                  --algo auto|one_shot|two_shot] train-images train-labels test-images test-labels
+//   cudampi -np N [--rate 0.1 --nepoch 10 --batch-size 256 --seed 0 --log-every 1000 --synthetic M --synthetic-test M
+//                  --pool --backend auto|simt|tcgen05 --save F --load F --timing
+//                  --algo auto|one_shot|two_shot|ll_one_shot|ll_two_shot] train-images train-labels test-images test-labels
 #include <cuda_runtime.h>
 #include <sys/mman.h>
 #include <sys/wait.h>
 #include <unistd.h>
 
 #include <chrono>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <string>
-#include <vector>
 
 #include "../cpu/comm.hpp"
-#include "../cpu/idx.hpp"
-#include "../cpu/net.hpp"
-#include "b200cnn.h"
-#include "b200cnn_comm.h"
+#include "gpu_app_common.hpp"
 
 using namespace b200cnn;
 
 namespace {
 
-struct Options {
-    double rate = 0.1;
-    int nepoch = 10, batch = 256, log_every = 1000, synthetic = 0, np = 0, algo = B200CNN_ALGO_AUTO;
-    unsigned seed = 0;
-    bool timing = false;
-    std::vector<std::string> pos;
-};
-
 struct Shared {  // host-side rendezvous area, mapped before fork()
     unsigned char handles[B200CNN_COMM_MAX_RANKS][64];
-    int failed;
 };
 
+// Any early exit tells the peers (ShmComm::abort): they are, or soon will be, waiting for this rank in a barrier.
+#define FAIL(code)      \
+    do {                \
+        host.abort();   \
+        return (code);  \
+    } while (0)
 #define CK(call)                                                                                   \
     do {                                                                                           \
         int rc__ = (call);                                                                         \
         if (rc__) {                                                                                \
             fprintf(stderr, "rank %d: %s failed (%d): %s\n", rank, #call, rc__, b200cnn_last_error()); \
-            return 1;                                                                              \
+            FAIL(1);                                                                               \
         }                                                                                          \
     } while (0)
 #define CU(call)                                                                                   \
@@ -55,32 +49,25 @@ struct Shared {  // host-side rendezvous area, mapped before fork()
         cudaError_t e__ = (call);                                                                  \
         if (e__ != cudaSuccess) {                                                                  \
             fprintf(stderr, "rank %d: %s failed: %s\n", rank, #call, cudaGetErrorString(e__));    \
-            return 1;                                                                              \
+            FAIL(1);                                                                               \
         }                                                                                          \
     } while (0)
 
-int run_rank(int rank, int world, const Options& o, Shared* sh, ShmComm& host) {
-    CU(cudaSetDevice(rank));
+int run_rank(int rank, int world, const app::Options& o, Shared* sh, ShmComm& host) {
     IdxFile tx, ty, ex, ey;
-    if (o.synthetic > 0 && o.pos.size() < 4) {
-        make_synthetic(uint32_t(o.synthetic), 28, 28, 10, 1, tx, ty);
-        make_synthetic(uint32_t(std::max(100, o.synthetic / 5)), 28, 28, 10, 2, ex, ey);
-    } else {
-        std::string err;
-        IdxFile* f[4] = {&tx, &ty, &ex, &ey};
-        for (int i = 0; i < 4; i++)
-            if (!idx_read(o.pos[i], *f[i], &err)) {
-                fprintf(stderr, "%s\n", err.c_str());
-                return 111;
-            }
+    if (int rc = app::load_data(o, tx, ty, ex, ey)) FAIL(rc);
+    int ngpu = 0;
+    if (cudaGetDeviceCount(&ngpu) != cudaSuccess || ngpu < world) {
+        if (rank == 0) fprintf(stderr, "cudampi: -np %d needs %d visible GPUs, found %d\n", world, world, ngpu);
+        FAIL(1);
     }
-    const b200cnn_layer_desc layers[6] = {{B200CNN_LAYER_INPUT, 1, 28, 28, 0, 0, 1},   {B200CNN_LAYER_CONV, 16, 14, 14, 3, 1, 2},
-                                          {B200CNN_LAYER_CONV, 32, 7, 7, 3, 1, 2},     {B200CNN_LAYER_FULL, 200, 1, 1, 0, 0, 1},
-                                          {B200CNN_LAYER_FULL, 200, 1, 1, 0, 0, 1},    {B200CNN_LAYER_FULL, 10, 1, 1, 0, 0, 1}};
-    b200cnn_engine* eng = b200cnn_engine_create(layers, 6, o.batch);
+    CU(cudaSetDevice(rank));
+    CK(b200cnn_set_backend(o.backend));
+    const std::vector<b200cnn_layer_desc> layers = app::topology(o.pool);
+    b200cnn_engine* eng = b200cnn_engine_create(layers.data(), int(layers.size()), o.batch);
     if (!eng) {
         fprintf(stderr, "rank %d: engine_create: %s\n", rank, b200cnn_last_error());
-        return 1;
+        FAIL(1);
     }
     // Peer-mapped region: allocate, publish the IPC handle, open everybody else's.
     const size_t flat = b200cnn_engine_flat_floats(eng);
@@ -88,7 +75,7 @@ int run_rank(int rank, int world, const Options& o, Shared* sh, ShmComm& host) {
     void* mine = b200cnn_ipc_alloc(bytes);
     if (!mine) {
         fprintf(stderr, "rank %d: ipc_alloc: %s\n", rank, b200cnn_last_error());
-        return 1;
+        FAIL(1);
     }
     CK(b200cnn_ipc_get_handle(mine, sh->handles[rank]));
     host.barrier();
@@ -97,25 +84,22 @@ int run_rank(int rank, int world, const Options& o, Shared* sh, ShmComm& host) {
         regions[r] = (r == rank) ? mine : b200cnn_ipc_open(sh->handles[r]);
         if (!regions[r]) {
             fprintf(stderr, "rank %d: ipc_open(%d): %s\n", rank, r, b200cnn_last_error());
-            return 1;
+            FAIL(1);
         }
     }
     host.barrier();
     b200cnn_comm* comm = b200cnn_comm_create(rank, world, regions, nullptr, flat);
     if (!comm) {
         fprintf(stderr, "rank %d: comm_create: %s\n", rank, b200cnn_last_error());
-        return 1;
+        FAIL(1);
     }
     CK(b200cnn_comm_set_algo(comm, o.algo));
     CK(b200cnn_engine_attach_comm(eng, comm));
 
-    // Reference initialisation on every rank, then rank 0's parameters over NVLink (the reference seeds per rank
-    // and never synchronises its replicas: SURVEY D7).
-    GlibcRand rng(o.seed);
-    Net cpu = Net::mnist(rng);
-    std::vector<double> p64;
-    cpu.gather_params(p64);
-    std::vector<float> p32(p64.begin(), p64.end());
+    // Reference initialisation (or the checkpoint) on every rank, then rank 0's parameters over NVLink (the reference
+    // seeds per rank and never synchronises its replicas: SURVEY D7).
+    std::vector<float> p32;
+    if (int rc = app::initial_params(o, b200cnn_engine_num_params(eng), p32)) FAIL(rc);
     CK(b200cnn_engine_set_params(eng, p32.data()));
     cudaStream_t st;
     CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
@@ -156,11 +140,18 @@ int run_rank(int rank, int world, const Options& o, Shared* sh, ShmComm& host) {
             // lr multiplies the batch-SUM gradient; the fused kernel divides by the world size.
             CK(b200cnn_engine_train_step(eng, xs, 1, ys, o.batch, float(o.rate / o.batch), 1, st));
             seen += o.batch;
-            if (rank == 0 && seen > next_log) {
-                CU(cudaMemcpyAsync(metrics, b200cnn_engine_metrics(eng), sizeof(metrics), cudaMemcpyDeviceToHost, st));
-                CU(cudaStreamSynchronize(st));
-                CK(b200cnn_engine_reset_metrics(eng, st));
-                if (metrics[3] > 0) fprintf(stderr, "    idx = %ld, error = %f\n", seen - o.batch, metrics[1] / metrics[3]);
+            if (seen > next_log) {
+                if (rank == 0) {
+                    CU(cudaMemcpyAsync(metrics, b200cnn_engine_metrics(eng), sizeof(metrics), cudaMemcpyDeviceToHost, st));
+                    CU(cudaStreamSynchronize(st));
+                    CK(b200cnn_engine_reset_metrics(eng, st));
+                    if (metrics[3] > 0) fprintf(stderr, "    idx = %ld, error = %f\n", seen - o.batch, metrics[1] / metrics[3]);
+                }
+                // a kernel that gave up waiting for a peer skipped its update: stop instead of training on
+                if (b200cnn_comm_error(comm)) {
+                    fprintf(stderr, "rank %d: a fused all-reduce timed out waiting for a peer\n", rank);
+                    FAIL(1);
+                }
                 next_log += std::max(o.log_every, o.batch);
             }
         }
@@ -170,17 +161,18 @@ int run_rank(int rank, int world, const Options& o, Shared* sh, ShmComm& host) {
     const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (b200cnn_comm_error(comm)) {
         fprintf(stderr, "rank %d: a fused all-reduce timed out waiting for a peer\n", rank);
-        return 1;
+        FAIL(1);
     }
     if (rank == 0 && o.timing && step)
         fprintf(stderr, "train_images_per_sec=%.1f (%ld samples, %d GPUs, %.3f s)\n", step * o.batch * world / dt, step * o.batch * world,
                 world, dt);
-    std::vector<float> fin(b200cnn_engine_num_params(eng));
-    CK(b200cnn_engine_get_params(eng, fin.data()));
+    CK(b200cnn_engine_get_params(eng, p32.data()));  // (waits for the peers' shares of the last update)
     double sum = 0;
-    for (float v : fin) sum += v;
+    for (float v : p32) sum += v;
     fprintf(stderr, "rank %d param_checksum=%.17g\n", rank, sum);
     if (rank == 0) {
+        if (!o.save_path.empty())
+            if (int rc = app::save_params(o.save_path, p32)) FAIL(rc);
         fprintf(stderr, "testing...\n");
         long ncorrect = 0;
         for (uint32_t i = 0; i < ntests; i += o.batch) {
@@ -206,29 +198,9 @@ int run_rank(int rank, int world, const Options& o, Shared* sh, ShmComm& host) {
 }  // namespace
 
 int main(int argc, char** argv) {
-    Options o;
-    for (int i = 1; i < argc; i++) {
-        const std::string a = argv[i];
-        auto val = [&]() -> const char* { return i + 1 < argc ? argv[++i] : nullptr; };
-        const char* v = nullptr;
-        if (a == "--rate") { if (!(v = val())) return 100; o.rate = atof(v); }
-        else if (a == "--nepoch") { if (!(v = val())) return 100; o.nepoch = atoi(v); }
-        else if (a == "--batch-size") { if (!(v = val())) return 100; o.batch = atoi(v); }
-        else if (a == "--seed") { if (!(v = val())) return 100; o.seed = unsigned(strtoul(v, nullptr, 10)); }
-        else if (a == "--log-every") { if (!(v = val())) return 100; o.log_every = atoi(v); }
-        else if (a == "--synthetic") { if (!(v = val())) return 100; o.synthetic = atoi(v); }
-        else if (a == "-np" || a == "--np") { if (!(v = val())) return 100; o.np = atoi(v); }
-        else if (a == "--algo") {
-            if (!(v = val())) return 100;
-            const std::string s = v;
-            o.algo = s == "one_shot" ? B200CNN_ALGO_ONE_SHOT : s == "two_shot" ? B200CNN_ALGO_TWO_SHOT : B200CNN_ALGO_AUTO;
-        }
-        else if (a == "--timing") o.timing = true;
-        else if (a.rfind("--", 0) == 0) { fprintf(stderr, "unknown option %s\n", a.c_str()); return 100; }
-        else o.pos.push_back(a);
-    }
-    if (o.synthetic <= 0 && o.pos.size() < 4) return 100;  // cnn.c:412
-    if (o.np < 1 || o.np > B200CNN_COMM_MAX_RANKS || o.batch < 1 || o.nepoch < 0) {
+    app::Options o;
+    if (int rc = app::parse(argc, argv, /*dp=*/true, o)) return rc;
+    if (o.np < 1 || o.np > B200CNN_COMM_MAX_RANKS) {
         fprintf(stderr, "usage: %s -np N (1..%d) [options] train-images train-labels test-images test-labels\n", argv[0], B200CNN_COMM_MAX_RANKS);
         return 100;
     }
@@ -245,7 +217,8 @@ int main(int argc, char** argv) {
         const pid_t pid = fork();
         if (pid < 0) {
             perror("fork");
-            return 111;
+            ShmComm::mark_failed(host_region);
+            break;
         }
         if (pid == 0) {
             ShmComm host(host_region, r, o.np);
@@ -253,12 +226,16 @@ int main(int argc, char** argv) {
         }
         kids.push_back(pid);
     }
-    int worst = 0;
-    for (pid_t pid : kids) {
+    // The first rank that ends badly releases the others from their barriers (they exit 112); report its code.
+    int first_bad = kids.size() == size_t(o.np) ? 0 : 111;
+    for (size_t left = kids.size(); left > 0; left--) {
         int stat = 0;
-        waitpid(pid, &stat, 0);
+        if (waitpid(-1, &stat, 0) < 0) break;
         const int rc = WIFEXITED(stat) ? WEXITSTATUS(stat) : 128 + WTERMSIG(stat);
-        if (rc > worst) worst = rc;
+        if (rc != 0) {
+            ShmComm::mark_failed(host_region);
+            if (first_bad == 0 || first_bad == kCommExit) first_bad = rc;
+        }
     }
-    return worst;
+    return first_bad;
 }

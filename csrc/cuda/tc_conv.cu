@@ -16,6 +16,8 @@
 //
 // Replaces Layer_feedForw_conv / the data half of Layer_feedBack_conv (cnn.c:175-247) and the
 // reference's only kernel, conv_forward_kernel (CUDAcnn.cu:167-195: scalar fp64, batch 1, no ReLU).
+#include <cstdlib>
+
 #include "backend.cuh"
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -38,12 +40,13 @@ struct ConvFwdArgs {
     int ldy;
     int n, oc, oh, ow, pad, group;  // group = samples per CTA
     int act;
+    int store_box;  // > 0: the epilogue stages the tile in shared memory and writes it with TMA boxes of this many floats
 };
 
 // ---- forward -------------------------------------------------------------------------------------
 template <int OC>
 __global__ void __launch_bounds__(kConvThreads, 1)
-tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a) {
+tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y, ConvFwdArgs a) {
     constexpr int kATile = kTileRows * kCin * 4;  // 8 KiB per tap (rows beyond group*oh*ow stay unused)
     constexpr int kBTile = OC * kCin * 4;         // OC rows x 64 B per tap
     constexpr int kTmemCols = OC < 32 ? 32 : OC;
@@ -62,6 +65,7 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a)
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_x);
+        if (a.store_box > 0) prefetch_tmap(&tmap_y);
         mbar_init(full_bar, 1);
         mbar_init(tmem_full_bar, 1);
         fence_barrier_init();
@@ -129,16 +133,53 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, ConvFwdArgs a)
         tcgen05_fence_after();
         const bool live = r < rows;
         const int g = r / pix, p = r % pix;
-        float* out = a.y + size_t(n0 + g) * a.ldy + p;
+        if (a.store_box > 0) {
+            // Epilogue through shared memory + TMA store: the A tiles are dead once the accumulator is complete, so
+            // the CHW-flattened output tile [group][oc * pix] is assembled there as boxes of `store_box` floats per
+            // sample ([box][sample][store_box], the dense layout a 2-D TMA box reads) and leaves the SM as a few bulk
+            // tensor stores instead of 32 strided 4-byte stores per thread.
+            float* stage = reinterpret_cast<float*>(a_tiles);
+            const int bw = a.store_box, per_box = a.group * bw;
 #pragma unroll
-        for (int c0 = 0; c0 < OC; c0 += 16) {
-            float v[16];
-            __syncwarp();
-            tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(c0), v);
-            if (live) {
+            for (int c0 = 0; c0 < OC; c0 += 32) {
+                float v[32];
+                __syncwarp();
+                if (OC - c0 >= 32) {
+                    tmem_ld_32x32b_x32(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(c0), v);
+                } else {
+                    float h[16];
+                    tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(c0), h);
 #pragma unroll
-                for (int i = 0; i < 16; i++)
-                    out[size_t(c0 + i) * pix] = apply_act(a.act, v[i] + bias[c0 + i]);
+                    for (int i = 0; i < 16; i++) v[i] = h[i];
+                }
+                if (live) {
+#pragma unroll
+                    for (int i = 0; i < (OC - c0 >= 32 ? 32 : 16); i++) {
+                        const int e = (c0 + i) * pix + p;  // position inside the sample's CHW-flattened output
+                        const int b = e / bw;
+                        stage[b * per_box + g * bw + (e - b * bw)] = apply_act(a.act, v[i] + bias[c0 + i]);
+                    }
+                }
+            }
+            fence_proxy_async_smem();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (threadIdx.x == 64) {
+                const int nbox = a.oc * pix / bw;
+                for (int b = 0; b < nbox; b++) tma_store_2d(&tmap_y, stage + b * per_box, b * bw, n0);  // rows past n are clipped
+                tma_store_commit_and_wait();
+            }
+        } else {
+            float* out = a.y + size_t(n0 + g) * a.ldy + p;
+#pragma unroll
+            for (int c0 = 0; c0 < OC; c0 += 16) {
+                float v[16];
+                __syncwarp();
+                tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(c0), v);
+                if (live) {
+#pragma unroll
+                    for (int i = 0; i < 16; i++)
+                        out[size_t(c0 + i) * pix] = apply_act(a.act, v[i] + bias[c0 + i]);
+                }
             }
         }
         __syncwarp();
@@ -374,7 +415,31 @@ int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y
                              uint32_t(group)};
     const uint32_t estr[4] = {1, uint32_t(s->stride), uint32_t(s->stride), 1};
     if (int rc = encode_tmap_f32(&tm, x_nhwc, 4, dims, strides, box, estr, 64)) return rc;
-    ConvFwdArgs a{w, b, y, ldy, s->n, s->oc, s->oh, s->ow, s->pad, group, act};
+    // Output through TMA: y seen as [n][oc * pix] with row stride ldy, written in boxes of `bw` floats x group samples
+    // (bw = the largest divisor of oc * pix that is a multiple of 4 and <= 256).  Needs 16-byte aligned rows.
+    int bw = 0;
+    const int per_sample = s->oc * pix;
+    static const bool tma_store = [] {
+        // Opt-in (B200CNN_TMA_STORE=1).  Correct (the whole GPU suite passes with it on) but measured SLOWER in the
+        // step on B200: 73.8 vs 71.4 us.  The plain stores are fire-and-forget and coalesce (consecutive lanes =
+        // consecutive pixels of one channel); the TMA path adds a shared-memory pass, a proxy fence, a CTA barrier and
+        // one thread issuing seven bulk stores at ~100 ns each to the tail of a kernel whose whole life is ~7 us.
+        const char* v = getenv("B200CNN_TMA_STORE");
+        return v && v[0] == '1';
+    }();
+    if (tma_store && ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0 && size_t(group) * per_sample * 4 <= size_t(kTaps) * kTileRows * kCin * 4)
+        for (int c = 256; c >= 4; c -= 4)
+            if (per_sample % c == 0) {
+                bw = c;
+                break;
+            }
+    CUtensorMap tmy = tm;
+    if (bw > 0) {
+        const uint64_t ydims[2] = {uint64_t(per_sample), uint64_t(s->n)}, ystr[2] = {0, uint64_t(ldy) * 4};
+        const uint32_t ybox[2] = {uint32_t(bw), uint32_t(group)};
+        if (int rc = encode_tmap_f32(&tmy, y, 2, ydims, ystr, ybox, nullptr, 0)) return rc;
+    }
+    ConvFwdArgs a{w, b, y, ldy, s->n, s->oc, s->oh, s->ow, s->pad, group, act, bw};
     const int grid = ceil_div(s->n, group);
 #define B200CNN_LAUNCH_FWD(OCV)                                                                                   \
     do {                                                                                                          \
@@ -385,7 +450,7 @@ int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y
             B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));      \
             configured = true;                                                                                    \
         }                                                                                                         \
-        B200CNN_CUDA(launch_kernel(kern, dim3(grid), dim3(kConvThreads), smem, st, tm, a));                          \
+        B200CNN_CUDA(launch_kernel(kern, dim3(grid), dim3(kConvThreads), smem, st, tm, tmy, a));                     \
     } while (0)
     if (s->oc == 16) B200CNN_LAUNCH_FWD(16);
     else if (s->oc == 32) B200CNN_LAUNCH_FWD(32);

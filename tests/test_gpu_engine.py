@@ -31,7 +31,7 @@ def test_forward_backward_step_vs_torch(pool, backend):
     # activations agree to <0.6 %, the conv weight / bias gradients (sums with heavy cancellation) to <4 % of their largest entry
     # (measured per tensor by tools/diag_engine.py: 0.3-2.2 %).
     tol = 2e-4 if backend == "simt" else 6e-3
-    gtol = 2e-4 if backend == "simt" else 4e-2
+    gtol = 2e-4 if backend == "simt" else 2.5e-2  # profiles/accuracy_vs_fp64.txt: worst tensor 1.1e-2 at batch 256
     B = 64
     eng = Engine(pool_layers() if pool else mnist_layers(), max_batch=B)
     cpu = eng.init_params(seed=0)
@@ -44,6 +44,9 @@ def test_forward_backward_step_vs_torch(pool, backend):
     L = len(eng.layers)
     assert _rel(eng.layer_output(L - 1, B), torch.softmax(feats[-1], 1).detach().cpu().numpy()) < tol
     assert _rel(eng.layer_output(L - 3, B), feats[2].detach().cpu().numpy()) < tol
+    # the second convolution's (pooled) activation: the tcgen05 implicit GEMM on the default topology
+    assert _rel(eng.layer_output(L - 4, B), feats[1].flatten(1).detach().cpu().numpy()) < tol
+    assert _rel(eng.layer_output(2 if pool else 1, B), feats[0].flatten(1).detach().cpu().numpy()) < tol
     m = eng.read_metrics()
     assert m["count"] == B
     assert m["mse_sum"] / B == pytest.approx(float(RefCNN.mse_metric(feats[-1].detach(), y)), rel=5e-3)

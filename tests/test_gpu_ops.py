@@ -4,12 +4,16 @@ Runs under both backends where the op has two implementations: 'simt' (CUDA core
 'tcgen05' (tensor cores, TF32 multiply, fp32 accumulate).  Tolerances: fp32 path 2e-4 relative to the
 output scale, TF32 path 4e-3 (10-bit mantissa operands).
 """
+import os
+
 import numpy as np
 import pytest
 import torch
 import torch.nn.functional as F
 
 pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 TOL = {"simt": 2e-4, "tcgen05": 4e-3, "auto": 4e-3}
 
@@ -336,3 +340,108 @@ def test_nhwc_conv2_weight_gradient(n, backend):
             stream.synchronize()
             _close(dw, want_w + 7.0 * acc, tol)
             _close(db, want_b + 7.0 * acc, tol)
+
+
+@pytest.mark.parametrize("n", [1, 3, 255, 256])
+@pytest.mark.parametrize("act", ["relu", "none"])
+def test_tcgen05_conv3x3_forward_direct(n, act):
+    """b200cnn_conv3x3_fwd_nhwc (the engine's tcgen05 implicit GEMM for the second convolution, 16 -> 32 channels,
+    14x14 -> 7x7, stride 2) against F.conv2d in fp32 with TF32 off.  NHWC input, CHW-flattened output with row stride
+    ldy; guard columns behind every output row must stay untouched."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    x = torch.randn(n, 16, 14, 14, device="cuda")
+    w, b = 0.2 * torch.randn(32, 16, 3, 3, device="cuda"), 0.1 * torch.randn(32, device="cuda")
+    want = F.conv2d(x, w, b, 2, 1)
+    if act == "relu":
+        want = torch.relu(want)
+    want = want.reshape(n, -1)
+    ldy = 32 * 49 + 8
+    y = torch.full((n, ldy), 7.0, device="cuda")
+    shp = N.ConvShape(n, 16, 14, 14, 32, 7, 7, 3, 1, 2)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    N.check(lib.b200cnn_conv3x3_fwd_nhwc(p(x.permute(0, 2, 3, 1).contiguous()), p(w), p(b), p(y), ldy, C.byref(shp),
+                                         N.ACT_RELU if act == "relu" else N.ACT_NONE, st), "conv3x3_fwd_nhwc")
+    torch.cuda.synchronize()
+    _close(y[:, :32 * 49], want, 4e-3)
+    assert bool((y[:, 32 * 49:] == 7.0).all())
+
+
+@pytest.mark.parametrize("n", [1, 3, 255, 256])
+@pytest.mark.parametrize("dz_is_chw", [0, 1])
+@pytest.mark.parametrize("mask", [True, False])
+def test_tcgen05_conv3x3s2_backward_data_direct(n, dz_is_chw, mask):
+    """b200cnn_conv3x3s2_bwd_data_nhwc (32 -> 16 channels, 7x7 -> 14x14) against conv_transpose2d in fp32 (TF32 off),
+    both gradient layouts, with and without the ReLU mask of the layer below."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dz = torch.randn(n, 32, 7, 7, device="cuda")
+    w = 0.2 * torch.randn(32, 16, 3, 3, device="cuda")
+    a_prev = torch.relu(torch.randn(n, 16, 14, 14, device="cuda"))
+    want = F.conv_transpose2d(dz, w, None, 2, 1, output_padding=1)
+    if mask:
+        want = want * (a_prev > 0)
+    dx = torch.full((n, 14, 14, 16), 7.0, device="cuda")
+    src = dz.contiguous() if dz_is_chw else dz.permute(0, 2, 3, 1).contiguous()
+    shp = N.ConvShape(n, 16, 14, 14, 32, 7, 7, 3, 1, 2)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    ap = a_prev.permute(0, 2, 3, 1).contiguous()
+    N.check(lib.b200cnn_conv3x3s2_bwd_data_nhwc(p(src), dz_is_chw, p(w), p(ap) if mask else None, N.ACT_RELU if mask else N.ACT_NONE, p(dx),
+                                                C.byref(shp), st), "conv3x3s2_bwd_data_nhwc")
+    torch.cuda.synchronize()
+    _close(dx.permute(0, 3, 1, 2), want, 4e-3)
+
+
+@pytest.mark.parametrize("n", [1, 2, 7, 64, 255, 256])
+@pytest.mark.parametrize("tc", ["1", "0"])
+def test_conv1_weight_gradient_direct(n, tc, monkeypatch):
+    """Weight / bias gradient of the first convolution (1 -> 16 channels, uint8 image) through
+    b200cnn_conv2d_bwd_weight_nhwc: the tcgen05 kernel (default) and the CUDA-core kernel (B200CNN_TC_C1=0 is read once
+    per process, so the second variant runs in a child process), against autograd; canaries around dw / db."""
+    import ctypes as C
+    import subprocess
+    import sys
+
+    if tc == "0":
+        code = ("import os,sys; os.environ['B200CNN_TC_C1']='0'; sys.path.insert(0, %r); import pytest; "
+                "sys.exit(pytest.main(['-q','-x','-m','gpu','-p','no:cacheprovider','%s::test_conv1_weight_gradient_direct[1-%d]']))"
+                % (ROOT, __file__, n))
+        if os.environ.get("B200CNN_TC_C1") == "0":
+            pytest.skip("already the CUDA-core child")
+        res = subprocess.run([sys.executable, "-c", code], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+        assert res.returncode == 0, res.stdout[-2000:]
+        return
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    torch.backends.cudnn.allow_tf32 = False
+    x = torch.randint(0, 256, (n, 1, 28, 28), device="cuda", dtype=torch.uint8)
+    dz = torch.randn(n, 16, 14, 14, device="cuda")
+    w = torch.zeros(16, 1, 3, 3, device="cuda", requires_grad=True)
+    F.conv2d(x.float() / 255.0, w, None, 2, 1).backward(dz)
+    want_w, want_b = w.grad, dz.sum((0, 2, 3))
+    shp = N.ConvShape(n, 1, 28, 28, 16, 14, 14, 3, 1, 2)
+    scratch = torch.zeros(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp)), dtype=torch.uint8, device="cuda")
+    buf = torch.full((16 * 9 + 16 + 64,), 7.0, device="cuda")
+    dw, db = buf[16:16 + 144], buf[16 + 144 + 16:16 + 144 + 32]
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for rep in range(2):  # the completion counter in the scratch header must reset itself
+        N.check(lib.b200cnn_conv2d_bwd_weight_nhwc(p(x), 1, p(dz.permute(0, 2, 3, 1).contiguous()), 0, p(dw), p(db), 0, p(scratch),
+                                                   C.byref(shp), st), "conv2d_bwd_weight_nhwc")
+        torch.cuda.synchronize()
+        _close(dw.reshape(16, 1, 3, 3), want_w, 4e-3)
+        _close(db, want_b, 4e-3)
+    assert bool((buf[:16] == 7.0).all()) and bool((buf[16 + 144:16 + 144 + 16] == 7.0).all()) and bool((buf[16 + 144 + 32:] == 7.0).all())
