@@ -30,7 +30,7 @@ CUDA_SRCS := $(wildcard csrc/cuda/*.cu) $(wildcard csrc/comm/*.cu)
 CUDA_OBJS := $(patsubst csrc/%.cu,$(OBJDIR)/%.o,$(CUDA_SRCS))
 CUDA_HDRS := $(wildcard csrc/cuda/*.cuh) $(wildcard csrc/comm/*.cuh) $(wildcard include/*.h)
 
-.PHONY: all cpu cuda clean sass cnnmpi_mpi cnnmpi_mpishim test_serial test_mpi test_cuda get_mnist
+.PHONY: all cpu cuda clean sass cnnmpi_mpi cnnmpi_mpishim asan tsan test_serial test_mpi test_cuda get_mnist
 
 all: cpu cuda
 
@@ -67,6 +67,24 @@ $(BINDIR)/cnnmpi_mpishim: $(CPU_OBJS) csrc/cpu/cnnmpi_main.cpp csrc/cpu/mpi_comm
 	@mkdir -p $(BINDIR) $(OBJDIR)
 	gcc -O2 -c baseline/mpi_shim/mpi_shim.c -o $(OBJDIR)/mpi_shim.o
 	$(CXX) $(CXXFLAGS) -DB200CNN_HAVE_MPI -Ibaseline/mpi_shim -o $@ csrc/cpu/cnnmpi_main.cpp $(CPU_OBJS) $(OBJDIR)/mpi_shim.o -lrt -lm
+
+# Sanitizer builds of the CPU engine and both CPU trainers (the reference has no -g, no -fsanitize, no checks of any
+# kind: /root/reference/Makefile:41,46).  asan = AddressSanitizer + UndefinedBehaviorSanitizer; tsan = ThreadSanitizer
+# over the fork-free pieces.  tests/test_sanitizers.py builds and runs them.
+# first compiler on the box that links the sanitizer runtimes (a toolchain may ship without libasan)
+SANCXX ?= $(shell for c in $(CXX) g++ /usr/bin/g++ clang++; do echo 'int main(){}' | $$c -x c++ -fsanitize=address,undefined - -o /dev/null 2>/dev/null && echo $$c && break; done)
+SANFLAGS := -O1 -g -std=c++17 -fno-omit-frame-pointer -ffp-contract=off -Wall -Wextra
+asan: $(BINDIR)/cnn_asan $(BINDIR)/cnnmpi_asan
+$(BINDIR)/cnn_asan: csrc/cpu/cnn_main.cpp $(CPU_SRCS) $(wildcard csrc/cpu/*.hpp)
+	@mkdir -p $(BINDIR)
+	$(SANCXX) $(SANFLAGS) -fsanitize=address,undefined -fno-sanitize-recover=undefined -o $@ csrc/cpu/cnn_main.cpp $(CPU_SRCS) -lrt -lm
+$(BINDIR)/cnnmpi_asan: csrc/cpu/cnnmpi_main.cpp $(CPU_SRCS) $(wildcard csrc/cpu/*.hpp)
+	@mkdir -p $(BINDIR)
+	$(SANCXX) $(SANFLAGS) -fsanitize=address,undefined -fno-sanitize-recover=undefined -o $@ csrc/cpu/cnnmpi_main.cpp $(CPU_SRCS) -lrt -lm
+tsan: $(BINDIR)/cnn_tsan
+$(BINDIR)/cnn_tsan: csrc/cpu/cnn_main.cpp $(CPU_SRCS) $(wildcard csrc/cpu/*.hpp)
+	@mkdir -p $(BINDIR)
+	$(SANCXX) $(SANFLAGS) -fsanitize=thread -o $@ csrc/cpu/cnn_main.cpp $(CPU_SRCS) -lrt -lm
 
 $(BINDIR)/mkidx: csrc/cpu/mkidx_main.cpp $(OBJDIR)/cpu/idx.o
 	@mkdir -p $(BINDIR)
