@@ -47,6 +47,12 @@ int tc_fc_chain(const float* x, int act_x, const float* w1, const float* b1, con
                 const float* b3, const uint8_t* labels, float* h1, float* h2, float* probs, float* dz3, float* dz2, float* dz1,
                 float* dx, float* metrics, int m, int k1, int n1, int n2, int nc, int ldc, cudaStream_t st);
 
+// ... and only its middle (same interface as tc_head): h2, softmax / loss, dz3, dz2, dz1 from h1 in one cluster kernel
+bool tc_fc_mid_supported(int m, int n1, int n2, int nc, int ldc);
+bool tc_fc_mid_enabled();
+int tc_fc_mid(const float* h1, const float* w2, const float* b2, const float* w3, const float* b3, const uint8_t* labels, float* h2,
+              float* probs, float* dz3, float* dz2, float* dz1, float* metrics, int m, int n1, int n2, int nc, int ldc, cudaStream_t st);
+
 // tc_conv.cu: implicit-GEMM 3x3 convolutions on NHWC activations
 bool tc_conv3x3_fwd_supported(const b200cnn_conv_shape* s);
 int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s,

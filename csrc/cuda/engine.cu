@@ -147,6 +147,16 @@ bool use_chain(const b200cnn_engine* e, int batch) {
     return tc_fc_chain_supported(batch, L[n - 4].nnodes, L[n - 3].nnodes, L[n - 2].nnodes, L[n - 1].nnodes, L[n - 1].ld);
 }
 
+// Same topology test for the cluster kernel that fuses only the middle (fc -> softmax/loss -> two data-gradient GEMMs).
+bool use_mid(const b200cnn_engine* e, int batch) {
+    const auto& L = e->layers;
+    const size_t n = L.size();
+    if (n < 4 || !tc_fc_mid_enabled()) return false;
+    for (size_t i = n - 3; i < n; i++)
+        if (L[i].d.type != B200CNN_LAYER_FULL) return false;
+    return tc_fc_mid_supported(batch, L[n - 3].nnodes, L[n - 2].nnodes, L[n - 1].nnodes, L[n - 1].ld);
+}
+
 // Forward through layers [1, stop).
 int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
                     cudaStream_t st, int* launches, size_t stop = ~size_t(0)) {
@@ -663,7 +673,8 @@ extern "C" int b200cnn_engine_sgd(b200cnn_engine* e, float lr, b200cnn_stream st
 static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
                         cudaStream_t st, int* launches, bool update = true) {
     const bool chain = use_chain(e, batch);
-    const bool head = !chain && use_head(e, batch);
+    const bool mid = !chain && use_mid(e, batch);
+    const bool head = !chain && (mid || use_head(e, batch));
     if (e->comm)
         if (int rc = comm_begin_step(e->comm, st)) return rc;
     if (chain) {
@@ -688,8 +699,9 @@ static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const 
         const size_t n = L.size();
         if (int rc = enqueue_forward(e, images, is_u8, labels, batch, st, launches, n - 2)) return rc;
         EngineLayer &l1 = L[n - 3], &l2 = L[n - 2], &l3 = L[n - 1];
-        if (int rc = tc_head(l1.a, e->params + l2.w_off, e->params + l2.b_off, e->params + l3.w_off, e->params + l3.b_off, labels, l2.a,
-                             l3.a, l3.dz, l2.dz, l1.dz, e->metrics, batch, l1.nnodes, l2.nnodes, l3.nnodes, l3.ld, st))
+        if (int rc = (mid ? tc_fc_mid : tc_head)(l1.a, e->params + l2.w_off, e->params + l2.b_off, e->params + l3.w_off, e->params + l3.b_off,
+                                                 labels, l2.a, l3.a, l3.dz, l2.dz, l1.dz, e->metrics, batch, l1.nnodes, l2.nnodes, l3.nnodes,
+                                                 l3.ld, st))
             return rc;
         if (launches) (*launches)++;
     }

@@ -46,12 +46,14 @@ constexpr int kQuads = kMaxSlice / 4;
 // NB = samples per cluster = UMMA N.  A B200 holds at most 15 clusters of 8 CTAs with this much shared memory
 // (cudaOccupancyMaxActiveClusters), so a batch of 256 runs as 11 clusters of 24 samples in ONE wave instead of 16
 // clusters of 16 in two; smaller batches use 16.
-template <int NB>
+// MID: only the four GEMMs in the middle (h1 comes from global memory, the chain ends with dz1): no W1 ring, half the
+// shared memory, so two CTAs share an SM and the kernel overlaps its neighbours in the stream.
+template <int NB, bool MID = false>
 struct Cfg {
     static constexpr int kTileB = NB * 128;   // one K block of a B operand (NB samples x 32 floats)
     // ring stage.  GEMM 1: x tile | W1 rows 0-127 16 KiB | W1 rows 128.. <= 10 KiB;  GEMM 6: up to seven 4 KiB groups
     static constexpr int kStage = (kTileB + 16384 + 10240) > 28672 ? (kTileB + 16384 + 10240) : 28672;
-    static constexpr int kStages = NB <= 16 ? 4 : 3;
+    static constexpr int kStages = MID ? 0 : (NB <= 16 ? 4 : 3);
     // shared memory map (bytes from the 1 KiB-aligned base)
     static constexpr int kOffRing = 0;
     static constexpr int kOffW2k = kOffRing + kStages * kStage;   // 7 x 4 KiB  W2 rows [s2*c, +32), K-major      (GEMM 2 A)
@@ -66,7 +68,7 @@ struct Cfg {
     static constexpr int kOffStg = kOffH2s + kMaxSlice * NB * 4;  // [28][NB] transposition buffer of epilogues 4 and 5
     static constexpr int kOffSmx = kOffStg + kMaxSlice * NB * 4;  // [16][NB + 1] logits, class-major, for the per-sample softmax
     static constexpr int kOffBars = (kOffSmx + 16 * (NB + 1) * 4 + 63) & ~63;
-    static constexpr int kNumBars = 2 * kStages + 1 + 7 + 5 + 1;
+    static constexpr int kNumBars = 2 * kStages + 1 + 7 + 5 + 1 + 1;
     static constexpr size_t kSmem = size_t(kOffBars) + kNumBars * 8 + 16 + 1024;
     static_assert(kSmem <= 227 * 1024, "shared memory budget");
     static_assert(CL * kMaxSlice * NB * 4 <= kMaxKB * kTileB, "GEMM-1 partials must fit the tile they borrow");
@@ -147,13 +149,15 @@ __device__ __forceinline__ uint32_t tile_off(int n, int k) {
     return uint32_t((k >> 5) * (NB * 128) + n * 128 + ((((k & 31) >> 2) ^ (n & 7)) << 4) + (k & 3) * 4);
 }
 
-template <int NB>
+template <int NB, bool MID>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w1a,
                    const __grid_constant__ CUtensorMap tm_w1b, const __grid_constant__ CUtensorMap tm_w1m,
                    const __grid_constant__ CUtensorMap tm_w2k, const __grid_constant__ CUtensorMap tm_w2m,
-                   const __grid_constant__ CUtensorMap tm_w3k, const __grid_constant__ CUtensorMap tm_w3m, ChainArgs a) {
-    using C = Cfg<NB>;
+                   const __grid_constant__ CUtensorMap tm_w3k, const __grid_constant__ CUtensorMap tm_w3m,
+                   const __grid_constant__ CUtensorMap tm_h1, ChainArgs a) {
+    using C = Cfg<NB, MID>;
+    const int stop = MID ? (a.stop < 5 ? a.stop : 5) : a.stop;  // MID ends with dz1 (epilogue 5 stores to global memory only)
     constexpr int kStages = C::kStages, kStage = C::kStage, kTileB = C::kTileB;
     constexpr int kOffRing = C::kOffRing, kOffW2k = C::kOffW2k, kOffW2m = C::kOffW2m, kOffW3k = C::kOffW3k, kOffW3m = C::kOffW3m;
     constexpr int kOffT0 = C::kOffT0, kOffT1 = C::kOffT1, kOffZ3 = C::kOffZ3;
@@ -167,7 +171,8 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
     uint64_t* acc_bar = wbar + 1;            // [7] accumulators complete: GEMM 1 (both tiles), GEMMs 2-5, GEMM 6 (both tiles)
     uint64_t* xbar = acc_bar + 7;            // [5] cluster-wide: all 8 CTAs have delivered their part (0: partials, 1-4: tiles)
     uint64_t* z3_bar = xbar + 5;             // the softmax has written the dz3 tile
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z3_bar + 1);
+    uint64_t* tile_bar = z3_bar + 1;         // MID: the h1 tile has landed from global memory
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tile_bar + 1);
     float* red = reinterpret_cast<float*>(smem + kOffT1);    // [CL src][kMaxSlice][NB]
     float* h1s = reinterpret_cast<float*>(smem + C::kOffH1s);
     float* h2s = reinterpret_cast<float*>(smem + C::kOffH2s);
@@ -201,6 +206,8 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         for (int i = 0; i < 7; i++) mbar_init(&acc_bar[i], 1);
         for (int i = 0; i < 5; i++) mbar_init(&xbar[i], CL);
         mbar_init(z3_bar, 1);
+        mbar_init(tile_bar, 1);
+        if (MID) prefetch_tmap(&tm_h1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
@@ -215,67 +222,81 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 
     if (warp == 0) {
         // ===== ring producer: small weights, GEMM 1's share of W1 and x, then W1's M-major view for GEMM 6 =====
-        if (lane == 0 && a.stop >= 1) {
+        if (lane == 0 && stop >= 1) {
+            if constexpr (MID) {
+                // small weights, then this cluster's h1 tile (all n1 features of its NB samples) as the first B operand
+                mbar_arrive_expect_tx(wbar, uint32_t(kbh1 * 4096 + kbh2 * 4096 + kbh2 * 2048 + 2048));
+                for (int k = 0; k < kbh1; k++) tma_load_2d(smem + kOffW2k + k * 4096, &tm_w2k, wbar, k * 32, f2);
+                mbar_arrive_expect_tx(tile_bar, uint32_t(kbh1 * kTileB));
+                for (int k = 0; k < kbh1; k++) tma_load_2d(smem + kOffT0 + k * kTileB, &tm_h1, tile_bar, k * 32, n0);
+                for (int k = 0; k < kbh2; k++) tma_load_2d(smem + kOffW3k + k * 2048, &tm_w3k, wbar, k * 32, 0);
+                tma_load_2d(smem + kOffW3m, &tm_w3m, wbar, f2, 0);
+                for (int k = 0; k < kbh2; k++) tma_load_2d(smem + kOffW2m + k * 4096, &tm_w2m, wbar, f1, k * 32);
+            } else {
             // GEMM 1's first stages go out first (they are the head of the critical path), then the small weights
-            // (needed from GEMM 2 on), then the rest of the ring traffic as slots come free.
-            int fill = 0;
-            const uint32_t rows_b = uint32_t(a.n1 > 128 ? ((a.n1 - 128 + 7) & ~7) : 0);  // box rows of W1's second tile
-            auto gemm1_stage = [&](int kb) {
-                const int s = fill % kStages;
-                mbar_wait(&empty[s], ((fill / kStages) & 1) ^ 1);
-                uint8_t* st = smem + kOffRing + s * kStage;
-                mbar_arrive_expect_tx(&full[s], uint32_t(kTileB + 16384 + rows_b * 128));
-                tma_load_2d(st, &tm_x, &full[s], kb * 32, n0);
-                tma_load_2d(st + kTileB, &tm_w1a, &full[s], kb * 32, 0);
-                if (rows_b) tma_load_2d(st + kTileB + 16384, &tm_w1b, &full[s], kb * 32, 128);
-                fill++;
-            };
-            int kb = kbA;
-            for (; kb < kbB && fill < kStages; kb++) gemm1_stage(kb);
-            mbar_arrive_expect_tx(wbar, uint32_t(kbh1 * 4096 + kbh2 * 4096 + kbh2 * 2048 + 2048));
-            for (int k = 0; k < kbh1; k++) tma_load_2d(smem + kOffW2k + k * 4096, &tm_w2k, wbar, k * 32, f2);
-            for (int k = 0; k < kbh2; k++) tma_load_2d(smem + kOffW3k + k * 2048, &tm_w3k, wbar, k * 32, 0);
-            tma_load_2d(smem + kOffW3m, &tm_w3m, wbar, f2, 0);
-            for (int k = 0; k < kbh2; k++) tma_load_2d(smem + kOffW2m + k * 4096, &tm_w2m, wbar, f1, k * 32);
-            for (; kb < kbB; kb++) gemm1_stage(kb);
-            CHAIN_STAMP(1);
-            for (int kb = 0; kb < kbh1 && a.stop >= 6 && xt > 0; kb++, fill++) {
-                const int s = fill % kStages;
-                mbar_wait(&empty[s], ((fill / kStages) & 1) ^ 1);
-                uint8_t* st = smem + kOffRing + s * kStage;
-                mbar_arrive_expect_tx(&full[s], uint32_t(xg * 4096));
-                for (int g = 0; g < xg; g++) tma_load_2d(st + g * 4096, &tm_w1m, &full[s], j0 + 32 * g, kb * 32);
+                // (needed from GEMM 2 on), then the rest of the ring traffic as slots come free.
+                int fill = 0;
+                const uint32_t rows_b = uint32_t(a.n1 > 128 ? ((a.n1 - 128 + 7) & ~7) : 0);  // box rows of W1's second tile
+                auto gemm1_stage = [&](int kb) {
+                    const int s = fill % kStages;
+                    mbar_wait(&empty[s], ((fill / kStages) & 1) ^ 1);
+                    uint8_t* st = smem + kOffRing + s * kStage;
+                    mbar_arrive_expect_tx(&full[s], uint32_t(kTileB + 16384 + rows_b * 128));
+                    tma_load_2d(st, &tm_x, &full[s], kb * 32, n0);
+                    tma_load_2d(st + kTileB, &tm_w1a, &full[s], kb * 32, 0);
+                    if (rows_b) tma_load_2d(st + kTileB + 16384, &tm_w1b, &full[s], kb * 32, 128);
+                    fill++;
+                };
+                int kb = kbA;
+                for (; kb < kbB && fill < kStages; kb++) gemm1_stage(kb);
+                mbar_arrive_expect_tx(wbar, uint32_t(kbh1 * 4096 + kbh2 * 4096 + kbh2 * 2048 + 2048));
+                for (int k = 0; k < kbh1; k++) tma_load_2d(smem + kOffW2k + k * 4096, &tm_w2k, wbar, k * 32, f2);
+                for (int k = 0; k < kbh2; k++) tma_load_2d(smem + kOffW3k + k * 2048, &tm_w3k, wbar, k * 32, 0);
+                tma_load_2d(smem + kOffW3m, &tm_w3m, wbar, f2, 0);
+                for (int k = 0; k < kbh2; k++) tma_load_2d(smem + kOffW2m + k * 4096, &tm_w2m, wbar, f1, k * 32);
+                for (; kb < kbB; kb++) gemm1_stage(kb);
+                CHAIN_STAMP(1);
+                for (int kb = 0; kb < kbh1 && stop >= 6 && xt > 0; kb++, fill++) {
+                    const int s = fill % kStages;
+                    mbar_wait(&empty[s], ((fill / kStages) & 1) ^ 1);
+                    uint8_t* st = smem + kOffRing + s * kStage;
+                    mbar_arrive_expect_tx(&full[s], uint32_t(xg * 4096));
+                    for (int g = 0; g < xg; g++) tma_load_2d(st + g * 4096, &tm_w1m, &full[s], j0 + 32 * g, kb * 32);
+                }
             }
             CHAIN_STAMP(2);
         }
     } else if (warp == 1) {
         // ===== MMA issuer (one thread) =====
-        if (lane == 0 && a.stop >= 1) {
+        if (lane == 0 && stop >= 1) {
             constexpr uint32_t idesc_kk64 = make_idesc_tf32(64, NB, false, false);    // A K-major, B K-major, M = 64
             constexpr uint32_t idesc_mk64 = make_idesc_tf32(64, NB, true, false);     // A M-major, B K-major, M = 64
             constexpr uint32_t idesc_kk128 = make_idesc_tf32(128, NB, false, false);
             constexpr uint32_t idesc_mk128 = make_idesc_tf32(128, NB, true, false);
             const uint32_t ring = smem_u32(smem + kOffRing);
             int take = 0;
+            if (!MID) {
             // GEMM 1 (this CTA's K blocks, all n1 features): partial h1^T = W1[:, K part] x^T[K part]
-            for (int kb = kbA; kb < kbB; kb++, take++) {
-                const int s = take % kStages;
-                mbar_wait(&full[s], (take / kStages) & 1);
-                tcgen05_fence_after();
-                const uint32_t b_addr = ring + s * kStage, a_addr = b_addr + kTileB;
-                const int ksteps = min(4, (a.k1 - kb * 32 + 7) / 8);
-                for (int t = 0; t < t1; t++)
-                    for (int kk = 0; kk < ksteps; kk++)
-                        umma_tf32(tmem_base + 32 * t, make_smem_desc(a_addr + t * 16384 + kk * 32, 16, 1024, kSw128),
-                                  make_smem_desc(b_addr + kk * 32, 16, 1024, kSw128), idesc_kk128, (kb != kbA) || kk != 0);
-                umma_commit(&empty[s]);
+                for (int kb = kbA; kb < kbB; kb++, take++) {
+                    const int s = take % kStages;
+                    mbar_wait(&full[s], (take / kStages) & 1);
+                    tcgen05_fence_after();
+                    const uint32_t b_addr = ring + s * kStage, a_addr = b_addr + kTileB;
+                    const int ksteps = min(4, (a.k1 - kb * 32 + 7) / 8);
+                    for (int t = 0; t < t1; t++)
+                        for (int kk = 0; kk < ksteps; kk++)
+                            umma_tf32(tmem_base + 32 * t, make_smem_desc(a_addr + t * 16384 + kk * 32, 16, 1024, kSw128),
+                                      make_smem_desc(b_addr + kk * 32, 16, 1024, kSw128), idesc_kk128, (kb != kbA) || kk != 0);
+                    umma_commit(&empty[s]);
+                }
+                CHAIN_STAMP(3);
+                umma_commit(&acc_bar[0]);
             }
-            CHAIN_STAMP(3);
-            umma_commit(&acc_bar[0]);
             mbar_wait(wbar, 0);
-            if (a.stop < 2) goto mma_done;
+            if (stop < 2) goto mma_done;
             // GEMM 2: h2^T slice = W2[f2.., :] h1^T     (boundary 1: every CTA has written its h1 slice into T0)
-            mbar_wait_cluster(&xbar[1], 0);
+            if (MID) mbar_wait(tile_bar, 0);
+            else mbar_wait_cluster(&xbar[1], 0);
             CHAIN_STAMP(4);
             tcgen05_fence_after();
             for (int kb = 0; kb < kbh1; kb++) {
@@ -286,7 +307,7 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             }
             umma_commit(&acc_bar[1]);
             CHAIN_STAMP(5);
-            if (a.stop < 3) goto mma_done;
+            if (stop < 3) goto mma_done;
             // GEMM 3: logits^T = W3 h2^T (all classes, every CTA)
             mbar_wait_cluster(&xbar[2], 0);
             CHAIN_STAMP(6);
@@ -299,7 +320,7 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             }
             umma_commit(&acc_bar[2]);
             CHAIN_STAMP(7);
-            if (a.stop < 4) goto mma_done;
+            if (stop < 4) goto mma_done;
             // GEMM 4: (dz3 W3)^T slice = W3[:, f2..]^T dz3^T     (A M-major: 16 class rows x 32 features)
             mbar_wait(z3_bar, 0);
             CHAIN_STAMP(8);
@@ -308,7 +329,7 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 umma_tf32(tmem_base + 128, make_smem_desc(smem_u32(smem + kOffW3m) + kk * 1024, 4096, 512, kSw128Base32),
                           make_smem_desc(smem_u32(smem + kOffZ3) + kk * 32, 16, 1024, kSw128), idesc_mk64, kk != 0);
             umma_commit(&acc_bar[3]);
-            if (a.stop < 5) goto mma_done;
+            if (stop < 5) goto mma_done;
             // GEMM 5: (dz2 W2)^T slice = W2[:, f1..]^T dz2^T
             mbar_wait_cluster(&xbar[3], 0);
             CHAIN_STAMP(9);
@@ -321,27 +342,29 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             }
             umma_commit(&acc_bar[4]);
             CHAIN_STAMP(10);
-            if (a.stop < 6) goto mma_done;
+            if (stop < 6) goto mma_done;
+            if constexpr (!MID) {
             // GEMM 6: (dz1 W1)^T slice = W1[:, j0..]^T dz1^T, up to two M = 128 tiles; W1 arrives through the ring
-            mbar_wait_cluster(&xbar[4], 0);
-            CHAIN_STAMP(11);
-            tcgen05_fence_after();
-            for (int kb = 0; kb < kbh1 && xt > 0; kb++, take++) {
-                const int s = take % kStages;
-                mbar_wait(&full[s], (take / kStages) & 1);
+                mbar_wait_cluster(&xbar[4], 0);
+                CHAIN_STAMP(11);
                 tcgen05_fence_after();
-                const int ksteps = min(4, (a.n1 - kb * 32 + 7) / 8);
-                for (int t = 0; t < xt; t++)
-                    for (int kk = 0; kk < ksteps; kk++)
-                        umma_tf32(tmem_base + 192 + 32 * t, make_smem_desc(ring + s * kStage + t * 16384 + kk * 1024, 4096, 512, kSw128Base32),
-                                  make_smem_desc(smem_u32(smem + kOffT1 + kb * kTileB) + kk * 32, 16, 1024, kSw128), idesc_mk128, (kb | kk) != 0);
-                umma_commit(&empty[s]);
+                for (int kb = 0; kb < kbh1 && xt > 0; kb++, take++) {
+                    const int s = take % kStages;
+                    mbar_wait(&full[s], (take / kStages) & 1);
+                    tcgen05_fence_after();
+                    const int ksteps = min(4, (a.n1 - kb * 32 + 7) / 8);
+                    for (int t = 0; t < xt; t++)
+                        for (int kk = 0; kk < ksteps; kk++)
+                            umma_tf32(tmem_base + 192 + 32 * t, make_smem_desc(ring + s * kStage + t * 16384 + kk * 1024, 4096, 512, kSw128Base32),
+                                      make_smem_desc(smem_u32(smem + kOffT1 + kb * kTileB) + kk * 32, 16, 1024, kSw128), idesc_mk128, (kb | kk) != 0);
+                    umma_commit(&empty[s]);
+                }
+                umma_commit(&acc_bar[5]);
+                CHAIN_STAMP(12);
             }
-            umma_commit(&acc_bar[5]);
-            CHAIN_STAMP(12);
         mma_done:;
         }
-    } else if (a.stop >= 1) {
+    } else if (stop >= 1) {
         // ===== epilogue warps (128 threads) =====
         const int q = warp & 3;                       // TMEM lane quarter this warp may access
         const uint32_t tq = tmem_base + (uint32_t(32 * q) << 16);
@@ -383,49 +406,63 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             }
         };
 
+        if (!MID) {
         // ---- epilogue 1a: reduce-scatter the partial h1^T tiles (feature f goes to the CTA that owns slice f / s1) ----
-        mbar_wait(&acc_bar[0], 0);
-        if (e == 0) CHAIN_STAMP(13);
-        tcgen05_fence_after();
-        for (int t = 0; t < t1; t++) {
-            __syncwarp();
-            tmem_ld_row<NB>(tq + 32 * t, v);
-            if (kbA == kbB) {  // a short K gave this CTA no K block: its partial is zero, not an unwritten accumulator
+            mbar_wait(&acc_bar[0], 0);
+            if (e == 0) CHAIN_STAMP(13);
+            tcgen05_fence_after();
+            for (int t = 0; t < t1; t++) {
+                __syncwarp();
+                tmem_ld_row<NB>(tq + 32 * t, v);
+                if (kbA == kbB) {  // a short K gave this CTA no K block: its partial is zero, not an unwritten accumulator
 #pragma unroll
-                for (int i = 0; i < NB; i++) v[i] = 0.f;
+                    for (int i = 0; i < NB; i++) v[i] = 0.f;
+                }
+                const int f = 128 * t + 32 * q + lane;
+                if (f < a.n1) {
+                    const int d = f / s1, fl = f - d * s1;
+                    const uint32_t dst = map_to_cluster_rank(smem_u32(red + (size_t(c) * kMaxSlice + fl) * NB), uint32_t(d));
+#pragma unroll
+                    for (int i = 0; i < NB / 4; i++) st_cluster_f32x4(dst + 16 * i, v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                }
             }
-            const int f = 128 * t + 32 * q + lane;
-            if (f < a.n1) {
-                const int d = f / s1, fl = f - d * s1;
-                const uint32_t dst = map_to_cluster_rank(smem_u32(red + (size_t(c) * kMaxSlice + fl) * NB), uint32_t(d));
+            epi_bar_sync();
+            if (e < CL) mbar_arrive_remote(map_to_cluster_rank(smem_u32(&xbar[0]), uint32_t(e)));
+            mbar_wait_cluster(&xbar[0], 0);
+            if (e == 0) CHAIN_STAMP(14);
+            // ---- epilogue 1b: h1 slice = tanh(sum over the 8 partials in CTA order + b1) -> every CTA's T0 ----
+            for (int item = e; item < kItems; item += 128) {
+                const int n = item / kQuads, fq = item % kQuads;
+                const int k = f1 + 4 * fq;
+                if (4 * fq >= s1 || k >= a.n1) continue;
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int src = 0; src < CL; src++)
 #pragma unroll
-                for (int i = 0; i < NB / 4; i++) st_cluster_f32x4(dst + 16 * i, v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                    for (int i = 0; i < 4; i++) acc[i] += red[(size_t(src) * kMaxSlice + 4 * fq + i) * NB + n];
+                const float4 b = __ldg(reinterpret_cast<const float4*>(a.b1 + k));
+                const float4 h = make_float4(tanhf(acc[0] + b.x), tanhf(acc[1] + b.y), tanhf(acc[2] + b.z), tanhf(acc[3] + b.w));
+                h1s[(4 * fq + 0) * NB + n] = h.x;
+                h1s[(4 * fq + 1) * NB + n] = h.y;
+                h1s[(4 * fq + 2) * NB + n] = h.z;
+                h1s[(4 * fq + 3) * NB + n] = h.w;
+                scatter(kOffT0, f1, a.n1, a.h1, n, fq, h, stop >= 2);
+            }
+            if (stop >= 2) deliver(1);  // (its CTA barrier also orders everybody's reads of `red` = T1 before the peers may fill T1)
+        } else {
+            // MID: this CTA's slice of h1 (for 1 - h1^2 in epilogue 5) comes from global memory
+            for (int item = e; item < kItems; item += 128) {
+                const int n = item / kQuads, fq = item % kQuads;
+                const int k = f1 + 4 * fq;
+                if (4 * fq >= s1 || k >= a.n1) continue;
+                const float4 h = (n0 + n < a.m) ? __ldg(reinterpret_cast<const float4*>(a.h1 + size_t(n0 + n) * a.n1 + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                h1s[(4 * fq + 0) * NB + n] = h.x;
+                h1s[(4 * fq + 1) * NB + n] = h.y;
+                h1s[(4 * fq + 2) * NB + n] = h.z;
+                h1s[(4 * fq + 3) * NB + n] = h.w;
             }
         }
-        epi_bar_sync();
-        if (e < CL) mbar_arrive_remote(map_to_cluster_rank(smem_u32(&xbar[0]), uint32_t(e)));
-        mbar_wait_cluster(&xbar[0], 0);
-        if (e == 0) CHAIN_STAMP(14);
-        // ---- epilogue 1b: h1 slice = tanh(sum over the 8 partials in CTA order + b1) -> every CTA's T0 ----
-        for (int item = e; item < kItems; item += 128) {
-            const int n = item / kQuads, fq = item % kQuads;
-            const int k = f1 + 4 * fq;
-            if (4 * fq >= s1 || k >= a.n1) continue;
-            float acc[4] = {0.f, 0.f, 0.f, 0.f};
-            for (int src = 0; src < CL; src++)
-#pragma unroll
-                for (int i = 0; i < 4; i++) acc[i] += red[(size_t(src) * kMaxSlice + 4 * fq + i) * NB + n];
-            const float4 b = __ldg(reinterpret_cast<const float4*>(a.b1 + k));
-            const float4 h = make_float4(tanhf(acc[0] + b.x), tanhf(acc[1] + b.y), tanhf(acc[2] + b.z), tanhf(acc[3] + b.w));
-            h1s[(4 * fq + 0) * NB + n] = h.x;
-            h1s[(4 * fq + 1) * NB + n] = h.y;
-            h1s[(4 * fq + 2) * NB + n] = h.z;
-            h1s[(4 * fq + 3) * NB + n] = h.w;
-            scatter(kOffT0, f1, a.n1, a.h1, n, fq, h, a.stop >= 2);
-        }
-        if (a.stop >= 2) deliver(1);  // (its CTA barrier also orders everybody's reads of `red` = T1 before the peers may fill T1)
         if (e == 0) CHAIN_STAMP(15);
-        if (a.stop < 2) goto epi_done;
+        if (stop < 2) goto epi_done;
         // ---- epilogue 2: h2 slice = tanh(acc + b2) -> every CTA's T1 ----
         {
             const int g = f2 + r64;
@@ -445,12 +482,12 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             epi_bar_sync();
             for (int item = e; item < kItems; item += 128) {
                 const int n = item / kQuads, fq = item % kQuads;
-                if (4 * fq < s2 && f2 + 4 * fq < a.n2) scatter(kOffT1, f2, a.n2, a.h2, n, fq, quad(h2s, n, fq), a.stop >= 3);
+                if (4 * fq < s2 && f2 + 4 * fq < a.n2) scatter(kOffT1, f2, a.n2, a.h2, n, fq, quad(h2s, n, fq), stop >= 3);
             }
-            if (a.stop >= 3) deliver(2);
+            if (stop >= 3) deliver(2);
         }
         if (e == 0) CHAIN_STAMP(17);
-        if (a.stop < 3) goto epi_done;
+        if (stop < 3) goto epi_done;
         // ---- epilogue 3: softmax + loss gradient + metrics.  The warp of lane quarter 0 moves the logits (classes on
         //      lanes) to shared memory; NB of its threads then own one sample each (the whole row in registers) ----
         if (q == 0) {
@@ -527,7 +564,7 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 }
             }
         }
-        if (a.stop < 4) goto epi_done;
+        if (stop < 4) goto epi_done;
         // ---- epilogue 4: dz2 slice = acc * (1 - h2^2) -> every CTA's T0 ----
         mbar_wait(&acc_bar[3], 0);
         if (e == 0) CHAIN_STAMP(20);
@@ -537,11 +574,11 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         epi_bar_sync();
         for (int item = e; item < kItems; item += 128) {
             const int n = item / kQuads, fq = item % kQuads;
-            if (4 * fq < s2 && f2 + 4 * fq < a.n2) scatter(kOffT0, f2, a.n2, a.dz2, n, fq, quad(stg, n, fq), a.stop >= 5);
+            if (4 * fq < s2 && f2 + 4 * fq < a.n2) scatter(kOffT0, f2, a.n2, a.dz2, n, fq, quad(stg, n, fq), stop >= 5);
         }
-        if (a.stop >= 5) deliver(3);
+        if (stop >= 5) deliver(3);
         if (e == 0) CHAIN_STAMP(21);
-        if (a.stop < 5) goto epi_done;
+        if (stop < 5) goto epi_done;
         // ---- epilogue 5: dz1 slice = acc * (1 - h1^2) -> every CTA's T1 ----
         mbar_wait(&acc_bar[4], 0);
         if (e == 0) CHAIN_STAMP(22);
@@ -552,11 +589,11 @@ tc_fc_chain_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         epi_bar_sync();
         for (int item = e; item < kItems; item += 128) {
             const int n = item / kQuads, fq = item % kQuads;
-            if (4 * fq < s1 && f1 + 4 * fq < a.n1) scatter(kOffT1, f1, a.n1, a.dz1, n, fq, quad(stg, n, fq), a.stop >= 6);
+            if (4 * fq < s1 && f1 + 4 * fq < a.n1) scatter(kOffT1, f1, a.n1, a.dz1, n, fq, quad(stg, n, fq), stop >= 6);
         }
-        if (a.stop >= 6) deliver(4);
+        if (stop >= 6) deliver(4);
         if (e == 0) CHAIN_STAMP(23);
-        if (a.stop < 6) goto epi_done;
+        if (stop < 6) goto epi_done;
         // ---- epilogue 6: dx = acc * act'(x), up to two M = 128 tiles (row = TMEM lane) ----
         {
             float xv[NB];
@@ -652,22 +689,70 @@ int tc_fc_chain(const float* x, int act_x, const float* w1, const float* b1, con
     ChainArgs a{b1, b2, b3, labels, x, h1, h2, probs, dz3, dz2, dz1, dx, metrics, m, k1, n1, n2, nc, ldc, act_x, g_chain_stamps, stop};
     static bool configured = false;
     if (!configured) {
-        B200CNN_CUDA(cudaFuncSetAttribute(tc_fc_chain_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg<16>::kSmem)));
-        B200CNN_CUDA(cudaFuncSetAttribute(tc_fc_chain_kernel<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg<24>::kSmem)));
+        B200CNN_CUDA(cudaFuncSetAttribute(tc_fc_chain_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg<16>::kSmem)));
+        B200CNN_CUDA(cudaFuncSetAttribute(tc_fc_chain_kernel<24, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg<24>::kSmem)));
         configured = true;
     }
     const dim3 grid(1, ceil_div(m, nb), CL);
     if (wide)
-        B200CNN_CUDA(launch_kernel_cluster(tc_fc_chain_kernel<24>, grid, dim3(kThreads), Cfg<24>::kSmem, st, CL, tx, tw1a, tw1b, tw1m, tw2k,
-                                           tw2m, tw3k, tw3m, a));
+        B200CNN_CUDA(launch_kernel_cluster(tc_fc_chain_kernel<24, false>, grid, dim3(kThreads), Cfg<24>::kSmem, st, CL, tx, tw1a, tw1b, tw1m, tw2k,
+                                           tw2m, tw3k, tw3m, tx, a));
     else
-        B200CNN_CUDA(launch_kernel_cluster(tc_fc_chain_kernel<16>, grid, dim3(kThreads), Cfg<16>::kSmem, st, CL, tx, tw1a, tw1b, tw1m, tw2k,
-                                           tw2m, tw3k, tw3m, a));
+        B200CNN_CUDA(launch_kernel_cluster(tc_fc_chain_kernel<16, false>, grid, dim3(kThreads), Cfg<16>::kSmem, st, CL, tx, tw1a, tw1b, tw1m, tw2k,
+                                           tw2m, tw3k, tw3m, tx, a));
     B200CNN_CHECK_LAUNCH("tc_fc_chain");
     return 0;
 }
 
+// ---- the middle of the chain as its own kernel: h2, softmax / loss, dz3, dz2, dz1 from h1 ------------------------------
+bool tc_fc_mid_supported(int m, int n1, int n2, int nc, int ldc) { return tc_fc_chain_supported(m, 32, n1, n2, nc, ldc); }
+
+bool tc_fc_mid_enabled() {
+    static const bool on = [] {
+        // Opt-in (B200CNN_MID=1).  Correct (tests/test_gpu_ops.py::test_fc_mid_kernel) and three launches fewer, but the
+        // step is SLOWER with it on B200: 80.1 vs 71.8 us.  The four kernels it replaces overlap their neighbours'
+        // prologues and let the weight-gradient kernels of the side stream start one by one; the fused kernel releases
+        // all of them at once at its end, where they compete with the tail of the critical path.
+        const char* v = getenv("B200CNN_MID");
+        return v && v[0] == '1';
+    }();
+    return on && current_backend() != B200CNN_BACKEND_SIMT;
+}
+
+int tc_fc_mid(const float* h1, const float* w2, const float* b2, const float* w3, const float* b3, const uint8_t* labels, float* h2,
+              float* probs, float* dz3, float* dz2, float* dz1, float* metrics, int m, int n1, int n2, int nc, int ldc, cudaStream_t st) {
+    if (!tc_fc_mid_supported(m, n1, n2, nc, ldc)) return set_error(kInvalidValue, "tc_fc_mid: unsupported shape");
+    for (const void* p : {(const void*)h1, (const void*)w2, (const void*)w3, (const void*)h2, (const void*)dz2, (const void*)dz1})
+        if (reinterpret_cast<uintptr_t>(p) & 15) return set_error(kInvalidValue, "tc_fc_mid: operands must be 16-byte aligned");
+    constexpr int NB = 16;
+    CUtensorMap th1, tw2k, tw2m, tw3k, tw3m;
+    int rc = 0;
+    if ((rc = kmajor_map(&th1, h1, m, n1, n1, NB)) || (rc = kmajor_map(&tw2k, w2, n2, n1, n1, 32)) || (rc = mmajor_map(&tw2m, w2, n2, n1, n1, 32)) ||
+        (rc = kmajor_map(&tw3k, w3, nc, n2, n2, 16)) || (rc = mmajor_map(&tw3m, w3, nc, n2, n2, 16)))
+        return rc;
+    ChainArgs a{nullptr, b2, b3, labels, nullptr, const_cast<float*>(h1), h2, probs, dz3, dz2, dz1, nullptr, metrics, m, 32, n1, n2, nc, ldc,
+                B200CNN_ACT_NONE, g_chain_stamps, 99};
+    using C = Cfg<NB, true>;
+    static bool configured = false;
+    if (!configured) {
+        B200CNN_CUDA(cudaFuncSetAttribute(tc_fc_chain_kernel<NB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::kSmem)));
+        configured = true;
+    }
+    const dim3 grid(1, ceil_div(m, NB), CL);
+    // (the W1 / x maps of the full chain are unused here: the h1 map stands in for them)
+    B200CNN_CUDA(launch_kernel_cluster(tc_fc_chain_kernel<NB, true>, grid, dim3(kThreads), C::kSmem, st, CL, th1, th1, th1, th1, tw2k, tw2m, tw3k,
+                                       tw3m, th1, a));
+    B200CNN_CHECK_LAUNCH("tc_fc_mid");
+    return 0;
+}
+
 }  // namespace b200cnn
+
+extern "C" int b200cnn_fc_mid(const float* h1, const float* w2, const float* b2, const float* w3, const float* b3, const uint8_t* labels,
+                              float* h2, float* probs, float* dz3, float* dz2, float* dz1, float* metrics, int m, int n1, int n2, int nc,
+                              int ldc, b200cnn_stream stream) {
+    return b200cnn::tc_fc_mid(h1, w2, b2, w3, b3, labels, h2, probs, dz3, dz2, dz1, metrics, m, n1, n2, nc, ldc, b200cnn::as_stream(stream));
+}
 
 // How many clusters of the chain kernel the device can hold at once (cudaOccupancyMaxActiveClusters); a batch of more
 // than 16 x this many samples runs in waves.  -1 on error.
@@ -684,9 +769,9 @@ extern "C" int b200cnn_fc_chain_max_active_clusters(void) {
     attr[0].val.clusterDim.z = CL;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (cudaFuncSetAttribute(tc_fc_chain_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg<16>::kSmem)) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(tc_fc_chain_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg<16>::kSmem)) != cudaSuccess) return -1;
     int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, tc_fc_chain_kernel<16>, &cfg) != cudaSuccess) return -1;
+    if (cudaOccupancyMaxActiveClusters(&n, tc_fc_chain_kernel<16, false>, &cfg) != cudaSuccess) return -1;
     return n;
 }
 

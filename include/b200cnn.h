@@ -138,6 +138,14 @@ int b200cnn_fc_chain(const float* x, int act_x, const float* w1, const float* b1
                      float* dz2, float* dz1, float* dx, float* metrics, int m, int k1, int n1, int n2, int nc, int ldc,
                      b200cnn_stream stream);
 
+/* The four GEMMs in the middle of that chain as one cluster kernel (same arguments as b200cnn_mlp_head): from h1 it
+ * produces h2 = tanh(h1 W2^T + b2), probs / dz3 / metrics, dz2 = (dz3 W3)(1 - h2^2) and dz1 = (dz2 W2)(1 - h1^2).
+ * 8 <= n1, n2 <= 208 (multiples of 4), nc <= ldc <= 16.  Replaces Layer_feedForw_full x2 (cnn.c:113-152), the loss
+ * gradient + metric (cnn.c:275-286) and the error propagation of Layer_feedBack_full x2 (cnn.c:158-166). */
+int b200cnn_fc_mid(const float* h1, const float* w2, const float* b2, const float* w3, const float* b3, const uint8_t* labels,
+                   float* h2, float* probs, float* dz3, float* dz2, float* dz1, float* metrics, int m, int n1, int n2, int nc, int ldc,
+                   b200cnn_stream stream);
+
 /* ---- max pooling (K7; not in the reference) ------------------------------------------------ */
 int b200cnn_maxpool_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride,
                         b200cnn_stream stream);

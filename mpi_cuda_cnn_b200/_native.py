@@ -139,6 +139,7 @@ def cuda():
     _sig(lib, "b200cnn_linear_softmax_xent", i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, vp)
     _sig(lib, "b200cnn_mlp_head", i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_fc_chain", i, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp)
+    _sig(lib, "b200cnn_fc_mid", i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_maxpool_fwd", i, vp, vp, vp, i, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_maxpool_bwd", i, vp, vp, vp, i, vp, i, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_sgd_update", i, vp, vp, sz, f, i, vp)

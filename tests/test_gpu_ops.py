@@ -445,3 +445,38 @@ def test_conv1_weight_gradient_direct(n, tc, monkeypatch):
         _close(dw.reshape(16, 1, 3, 3), want_w, 4e-3)
         _close(db, want_b, 4e-3)
     assert bool((buf[:16] == 7.0).all()) and bool((buf[16 + 144:16 + 144 + 16] == 7.0).all()) and bool((buf[16 + 144 + 32:] == 7.0).all())
+
+
+@pytest.mark.parametrize("shape", [(256, 200, 200, 10), (16, 200, 200, 10), (37, 200, 200, 10), (5, 40, 24, 3), (130, 208, 120, 16), (300, 64, 200, 7)])
+def test_fc_mid_kernel(shape):
+    """The middle of the FC chain as its own cluster kernel (b200cnn_fc_mid: fc -> softmax/loss -> two data-gradient
+    GEMMs from h1) against PyTorch fp32 (TF32 off), twice in a row."""
+    import ctypes as C
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    m, n1, n2, nc = shape
+    torch.backends.cuda.matmul.allow_tf32 = False
+    h1 = torch.tanh(torch.randn(m, n1, device="cuda"))
+    w2, b2 = torch.randn(n2, n1, device="cuda") / n1 ** 0.5, 0.1 * torch.randn(n2, device="cuda")
+    w3, b3 = torch.randn(nc, n2, device="cuda") / n2 ** 0.5, 0.1 * torch.randn(nc, device="cuda")
+    lab = torch.randint(0, nc, (m,), device="cuda", dtype=torch.uint8)
+    rh2 = torch.tanh(h1 @ w2.T + b2)
+    rp = torch.softmax(rh2 @ w3.T + b3, 1)
+    rdz3 = rp - F.one_hot(lab.long(), nc)
+    rdz2 = (rdz3 @ w3) * (1 - rh2 ** 2)
+    rdz1 = (rdz2 @ w2) * (1 - h1 ** 2)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for rep in range(2):
+        h2, dz2 = torch.full((m, n2), 9.0, device="cuda"), torch.full((m, n2), 9.0, device="cuda")
+        pr, dz3 = torch.full((m, 16), 9.0, device="cuda"), torch.full((m, 16), 9.0, device="cuda")
+        dz1, met = torch.full((m, n1), 9.0, device="cuda"), torch.zeros(4, device="cuda")
+        N.check(lib.b200cnn_fc_mid(p(h1), p(w2), p(b2), p(w3), p(b3), p(lab), p(h2), p(pr), p(dz3), p(dz2), p(dz1), p(met), m, n1, n2, nc, 16, st), "fc_mid")
+        torch.cuda.synchronize()
+        for name, got, want in (("h2", h2, rh2), ("probs", pr[:, :nc], rp), ("dz3", dz3[:, :nc], rdz3), ("dz2", dz2, rdz2), ("dz1", dz1, rdz1)):
+            err = float((got - want).abs().max() / want.abs().max().clamp_min(1e-6))
+            assert err < 6e-3, (name, rep, err)
+        got = met.cpu().numpy()
+        assert got[3] == m and abs(got[2] - float((rp.argmax(1) == lab.long()).sum())) <= 1
+        assert got[0] == pytest.approx(float(-torch.log(rp[torch.arange(m), lab.long()]).sum()), rel=3e-3)
