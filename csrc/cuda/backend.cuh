@@ -56,7 +56,15 @@ int tc_fc_mid(const float* h1, const float* w2, const float* b2, const float* w3
 // tc_conv.cu: implicit-GEMM 3x3 convolutions on NHWC activations
 bool tc_conv3x3_fwd_supported(const b200cnn_conv_shape* s);
 int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s,
-                   int act, cudaStream_t st);
+                   int act, cudaStream_t st, int nhwc_out = 0);
+// stride-1 counterpart of tc_conv3x3s2_bwd_data (32 -> 16 channels, same spatial size): dz / a_prev / dx all NHWC
+bool tc_conv3x3s1_bwd_data_supported(const b200cnn_conv_shape* s);
+int tc_conv3x3s1_bwd_data(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
+                          const b200cnn_conv_shape* s, cudaStream_t st);
+// pool.cu: NHWC max pooling for the tensor-core chain of the pooled topology
+int maxpool_nhwc_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride, int out_chw, cudaStream_t st);
+int maxpool_nhwc_bwd(const float* dy, int dy_chw, const int32_t* argmax, const float* a_prev, int act_prev, float* dx, int n, int c,
+                     int h, int w, int k, int stride, cudaStream_t st);
 bool tc_conv3x3s2_bwd_data_supported(const b200cnn_conv_shape* s);
 int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
                           float* dx_nhwc, const b200cnn_conv_shape* s, cudaStream_t st);

@@ -71,6 +71,19 @@ extern "C" int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz, int dz_is_chw, c
     return tc_conv3x3s2_bwd_data(dz, dz_is_chw, w, a_prev_nhwc, act_prev, dx_nhwc, s, as_stream(stream));
 }
 
+// Same forward kernel with the output left NHWC [n][oh][ow][oc] (feeds a pooling / convolution layer instead of an FC layer).
+extern "C" int b200cnn_conv3x3_fwd_nhwc_to_nhwc(const float* x_nhwc, const float* w, const float* b, float* y_nhwc,
+                                                const b200cnn_conv_shape* s, int act, b200cnn_stream stream) {
+    if (!s || !tc_conv3x3_fwd_supported(s)) return set_error(kInvalidValue, "conv3x3_fwd_nhwc_to_nhwc: shape not supported by the tcgen05 path");
+    return tc_conv3x3_fwd(x_nhwc, w, b, y_nhwc, 0, s, act, as_stream(stream), 1);
+}
+
+extern "C" int b200cnn_conv3x3s1_bwd_data_nhwc(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev,
+                                               float* dx_nhwc, const b200cnn_conv_shape* s, b200cnn_stream stream) {
+    if (!s || !tc_conv3x3s1_bwd_data_supported(s)) return set_error(kInvalidValue, "conv3x3s1_bwd_data_nhwc: shape not supported by the tcgen05 path");
+    return tc_conv3x3s1_bwd_data(dz_nhwc, w, a_prev_nhwc, act_prev, dx_nhwc, s, as_stream(stream));
+}
+
 // dw (OIHW) / db of a convolution whose input x is NHWC (or a 1-channel image, uint8 allowed) and whose
 // output gradient is NHWC (or CHW when dz_is_chw).  scratch as for b200cnn_conv2d_bwd_weight.
 extern "C" int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const float* dz, int dz_is_chw, float* dw, float* db,

@@ -70,3 +70,85 @@ extern "C" int b200cnn_maxpool_bwd(const float* dy, const int32_t* argmax, const
     B200CNN_CHECK_LAUNCH("maxpool_bwd");
     return 0;
 }
+
+// ---- NHWC variants for the tensor-core convolution chain of the pooled topology -----------------------------------
+// x: NHWC [n][h][w][c]; y: NHWC [n][oh][ow][c], or (out_chw) CHW-flattened [n][c*oh*ow] — what a fully connected layer
+// reads (/root/reference/cnn.c:116-121).  argmax[n][oh][ow][c] = pixel index (yy * w + xx) of the winner.
+namespace b200cnn {
+namespace {
+
+__global__ void maxpool_nhwc_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int32_t* __restrict__ argmax, int n,
+                                        int c, int h, int w, int oh, int ow, int k, int stride, int out_chw) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;  // channel innermost: coalesced loads
+    if (i >= n * oh * ow * c) return;
+    const int ch = i % c, ox = (i / c) % ow, oy = (i / (c * ow)) % oh, s = i / (c * ow * oh);
+    const float* xp = x + size_t(s) * h * w * c + ch;
+    int best = -1;
+    float bv = 0.0f;
+    for (int dy = 0; dy < k; dy++)
+        for (int dx = 0; dx < k; dx++) {
+            const int idx = (oy * stride + dy) * w + ox * stride + dx;
+            const float v = __ldg(xp + size_t(idx) * c);
+            if (best < 0 || bv < v) {
+                best = idx;
+                bv = v;
+            }
+        }
+    const size_t o = out_chw ? (size_t(s) * c + ch) * oh * ow + oy * ow + ox : size_t(i);
+    y[o] = bv;
+    argmax[i] = best;
+}
+
+// dy: NHWC, or CHW-flattened when dy_chw; dx, a_prev: NHWC [n][h][w][c].  Gather form, no atomics.
+__global__ void maxpool_nhwc_bwd_kernel(const float* __restrict__ dy, int dy_chw, const int32_t* __restrict__ argmax,
+                                        const float* __restrict__ a_prev, int act_prev, float* __restrict__ dx, int n, int c, int h,
+                                        int w, int oh, int ow, int k, int stride) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * h * w * c) return;
+    const int ch = i % c, xx = (i / c) % w, yy = (i / (c * w)) % h, s = i / (c * w * h);
+    const int self = yy * w + xx;
+    float g = 0.0f;
+    const int oy_hi = min(yy / stride, oh - 1), ox_hi = min(xx / stride, ow - 1);
+    for (int oy = max(0, (yy - k + stride) / stride); oy <= oy_hi; oy++)
+        for (int ox = max(0, (xx - k + stride) / stride); ox <= ox_hi; ox++) {
+            const size_t o = ((size_t(s) * oh + oy) * ow + ox) * c + ch;
+            if (__ldg(argmax + o) == self) g += __ldg(dy + (dy_chw ? (size_t(s) * c + ch) * oh * ow + oy * ow + ox : o));
+        }
+    if (a_prev) g *= act_grad_from_output(act_prev, __ldg(a_prev + i));
+    dx[i] = g;
+}
+
+}  // namespace
+
+int maxpool_nhwc_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride, int out_chw,
+                     cudaStream_t st) {
+    if (n <= 0 || c <= 0 || k <= 0 || stride <= 0 || h < k || w < k || !argmax) return set_error(kInvalidValue, "maxpool_nhwc_fwd: bad shape");
+    const int oh = (h - k) / stride + 1, ow = (w - k) / stride + 1;
+    B200CNN_CUDA(launch_kernel(maxpool_nhwc_fwd_kernel, dim3(ceil_div(n * c * oh * ow, 256)), dim3(256), 0, st, x, y, argmax, n, c, h, w,
+                               oh, ow, k, stride, out_chw));
+    return 0;
+}
+
+int maxpool_nhwc_bwd(const float* dy, int dy_chw, const int32_t* argmax, const float* a_prev, int act_prev, float* dx, int n, int c,
+                     int h, int w, int k, int stride, cudaStream_t st) {
+    if (n <= 0 || c <= 0 || k <= 0 || stride <= 0 || h < k || w < k || !argmax) return set_error(kInvalidValue, "maxpool_nhwc_bwd: bad shape");
+    const int oh = (h - k) / stride + 1, ow = (w - k) / stride + 1;
+    B200CNN_CUDA(launch_kernel(maxpool_nhwc_bwd_kernel, dim3(ceil_div(n * c * h * w, 256)), dim3(256), 0, st, dy, dy_chw, argmax, a_prev,
+                               act_prev, dx, n, c, h, w, oh, ow, k, stride));
+    return 0;
+}
+
+}  // namespace b200cnn
+
+extern "C" int b200cnn_maxpool_nhwc_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride,
+                                        int out_chw, b200cnn_stream stream) {
+    return b200cnn::maxpool_nhwc_fwd(x, y, argmax, n, c, h, w, k, stride, out_chw, b200cnn::as_stream(stream));
+}
+extern "C" int b200cnn_maxpool_nhwc_bwd(const float* dy, int dy_chw, const int32_t* argmax, const float* a_prev, int act_prev, float* dx,
+                                        int n, int c, int h, int w, int k, int stride, b200cnn_stream stream) {
+    return b200cnn::maxpool_nhwc_bwd(dy, dy_chw, argmax, a_prev, act_prev, dx, n, c, h, w, k, stride, b200cnn::as_stream(stream));
+}

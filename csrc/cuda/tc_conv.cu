@@ -40,7 +40,11 @@ struct ConvFwdArgs {
     int ldy;
     int n, oc, oh, ow, pad, group;  // group = samples per CTA
     int act;
+    int stride;
     int store_box;  // > 0: the epilogue stages the tile in shared memory and writes it with TMA boxes of this many floats
+    int tiles;      // > 1: an image has more than 128 output pixels and is cut into `tiles` bands of oh_t output rows,
+    int oh_t;       //      one band (and one sample) per CTA; tiles == 1: oh_t = oh and `group` samples per CTA
+    int nhwc_out;   // output [n][oh][ow][oc] (feeds another NHWC layer) instead of CHW-flattened rows
 };
 
 // ---- forward -------------------------------------------------------------------------------------
@@ -59,9 +63,11 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
     const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
-    const int n0 = blockIdx.x * a.group;
-    const int pix = a.oh * a.ow;
-    const int rows = min(a.group, a.n - n0) * pix;
+    const int band = a.tiles > 1 ? int(blockIdx.x) % a.tiles : 0;      // which band of output rows of the image
+    const int n0 = a.tiles > 1 ? int(blockIdx.x) / a.tiles : int(blockIdx.x) * a.group;
+    const int pix = a.oh * a.ow;             // output pixels of an image
+    const int tpix = a.oh_t * a.ow;          // ... of this CTA's band (= pix when tiles == 1)
+    const int rows = min(a.group, a.n - n0) * tpix;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_x);
@@ -81,10 +87,10 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     if (warp == 0) {
         if (lane == 0) {
             // One barrier for the whole K extent: 9 tap boxes of group*oh*ow pixels x 64 B.
-            mbar_arrive_expect_tx(full_bar, uint32_t(kTaps * a.group * pix * kCin * 4));
+            mbar_arrive_expect_tx(full_bar, uint32_t(kTaps * a.group * tpix * kCin * 4));
 #pragma unroll
             for (int t = 0; t < kTaps; t++)
-                tma_load_4d(a_tiles + t * kATile, &tmap_x, full_bar, 0, t % 3 - a.pad, t / 3 - a.pad, n0);
+                tma_load_4d(a_tiles + t * kATile, &tmap_x, full_bar, 0, t % 3 - a.pad, band * a.oh_t * a.stride + t / 3 - a.pad, n0);
         }
     } else if (warp >= 2) {
         // Weights: OIHW -> per-tap K-major [oc][c] tiles in the 64-byte-swizzle layout
@@ -132,8 +138,24 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
         const bool live = r < rows;
-        const int g = r / pix, p = r % pix;
-        if (a.store_box > 0) {
+        const int g = r / tpix, p = band * tpix + r % tpix;  // sample of the group, pixel of the image
+        if (a.nhwc_out) {
+            // channels innermost: a thread owns all OC values of its pixel -> OC / 4 16-byte stores
+            float* out = a.y + (size_t(n0 + g) * pix + p) * OC;
+#pragma unroll
+            for (int c0 = 0; c0 < OC; c0 += 16) {
+                float v[16];
+                __syncwarp();
+                tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(c0), v);
+                if (live) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4)
+                        *reinterpret_cast<float4*>(out + c0 + i) =
+                            make_float4(apply_act(a.act, v[i] + bias[c0 + i]), apply_act(a.act, v[i + 1] + bias[c0 + i + 1]),
+                                        apply_act(a.act, v[i + 2] + bias[c0 + i + 2]), apply_act(a.act, v[i + 3] + bias[c0 + i + 3]));
+                }
+            }
+        } else if (a.store_box > 0) {
             // Epilogue through shared memory + TMA store: the A tiles are dead once the accumulator is complete, so
             // the CHW-flattened output tile [group][oc * pix] is assembled there as boxes of `store_box` floats per
             // sample ([box][sample][store_box], the dense layout a 2-D TMA box reads) and leaves the SM as a few bulk
@@ -395,23 +417,157 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
     }
 }
 
+// ---- backward-data (3x3, stride 1, pad 1): the pooled topology's second convolution ------------------------------
+// dx[n][y][x][c] = act'(a_prev) * sum_tap sum_oc dz[n][y+1-ky][x+1-kx][oc] w[oc][c][ky][kx]: a plain 3x3 convolution of
+// dz with the taps mirrored.  Same implicit GEMM as the forward kernel — per tap ONE TMA box of the NHWC gradient
+// (32 channels = one 128-byte swizzle row per pixel, out-of-bounds = zero padding), B = the tap's [c][oc] weights —
+// 9 taps x 4 MMAs into one accumulator.  An image has 196 pixels, so it is cut into bands of whole rows (<= 128 pixels).
+struct ConvS1BwdArgs {
+    const float* w;       // OIHW [oc][c][3][3]
+    const float* a_prev;  // NHWC [n][h][w][c] or NULL
+    float* dx;            // NHWC [n][h][w][c]
+    int n, h, w_in, tiles, h_t;
+    int act_prev;
+};
+
+template <int OC, int C>
+__global__ void __launch_bounds__(kConvThreads, 1)
+tc_conv3x3s1_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvS1BwdArgs a) {
+    static_assert(OC == 32, "one 128-byte row of dz per pixel");
+    constexpr int kATile = kTileRows * OC * 4;  // 16 KiB per tap
+    constexpr int kBTile = C * OC * 4;          // [c rows][oc] per tap, 128-byte rows
+    constexpr int kTmemCols = 32;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* a_tiles = smem;
+    uint8_t* b_tiles = smem + kTaps * kATile;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + kTaps * kBTile);
+    uint64_t* tmem_full_bar = full_bar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+    const int band = int(blockIdx.x) % a.tiles, n0 = int(blockIdx.x) / a.tiles;
+    const int rows = a.h_t * a.w_in;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_dz);
+        mbar_init(full_bar, 1);
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(full_bar, uint32_t(kTaps * rows * OC * 4));
+#pragma unroll
+            for (int t = 0; t < kTaps; t++)  // tap (ky, kx) reads dz at (y + 1 - ky, x + 1 - kx)
+                tma_load_4d(a_tiles + t * kATile, &tmap_dz, full_bar, 0, 1 - t % 3, band * a.h_t + 1 - t / 3, n0);
+        }
+    } else if (warp >= 2) {
+        // Weights per tap as the B operand [n = c][k = oc], K-major 128-byte rows, 128B swizzle (chunk ^= row & 7).
+        constexpr int kW = OC * C * kTaps, kStride = kConvThreads - 64;
+        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += 4 * kStride) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i = i0 + u * kStride;
+                if (i >= kW) break;
+                const int t = i % kTaps, c = (i / kTaps) % C, oc = i / (kTaps * C);
+                const int chunk = (oc >> 2) ^ (c & 7);
+                *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = v[u];
+            }
+        }
+        fence_proxy_async_smem();
+    }
+    __syncthreads();
+
+    if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_tf32(kTileRows, C, false, false);
+            mbar_wait(full_bar, 0);
+            tcgen05_fence_after();
+            const uint32_t a_addr = smem_u32(a_tiles), b_addr = smem_u32(b_tiles);
+#pragma unroll
+            for (int t = 0; t < kTaps; t++)
+#pragma unroll
+                for (int kk = 0; kk < OC / 8; kk++)
+                    umma_tf32(tmem_base, make_smem_desc(a_addr + t * kATile + kk * 32, 16, 1024, kSw128),
+                              make_smem_desc(b_addr + t * kBTile + kk * 32, 16, 1024, kSw128), idesc, (t | kk) != 0);
+            umma_commit(tmem_full_bar);
+        }
+    } else if (warp >= 2) {
+        const int q = warp & 3;
+        const int r = 32 * q + lane;
+        const bool live = r < rows;
+        const size_t off = (size_t(n0) * a.h * a.w_in + size_t(band) * rows + r) * C;
+        float4 msk[C / 4];
+        if (live && a.a_prev) {
+#pragma unroll
+            for (int k4 = 0; k4 < C / 4; k4++) msk[k4] = __ldg(reinterpret_cast<const float4*>(a.a_prev + off) + k4);
+        }
+        mbar_wait(tmem_full_bar, 0);
+        tcgen05_fence_after();
+        float v[16];
+        tmem_ld_32x32b_x16(tmem_base + (uint32_t(32 * q) << 16), v);
+        if (live) {
+            if (a.a_prev) {
+#pragma unroll
+                for (int k4 = 0; k4 < C / 4; k4++) {
+                    v[4 * k4 + 0] *= act_grad_from_output(a.act_prev, msk[k4].x);
+                    v[4 * k4 + 1] *= act_grad_from_output(a.act_prev, msk[k4].y);
+                    v[4 * k4 + 2] *= act_grad_from_output(a.act_prev, msk[k4].z);
+                    v[4 * k4 + 3] *= act_grad_from_output(a.act_prev, msk[k4].w);
+                }
+            }
+            float4* dp = reinterpret_cast<float4*>(a.dx + off);
+#pragma unroll
+            for (int k4 = 0; k4 < C / 4; k4++) dp[k4] = make_float4(v[4 * k4], v[4 * k4 + 1], v[4 * k4 + 2], v[4 * k4 + 3]);
+        }
+        __syncwarp();
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
 }  // namespace
 
+// Bands an image is cut into so that a band has at most 128 output pixels (0: no such cut with whole rows).
+static int fwd_tiles(const b200cnn_conv_shape* s) {
+    if (s->oh * s->ow <= kTileRows) return 1;
+    for (int t = 2; t <= s->oh; t++)
+        if (s->oh % t == 0 && (s->oh / t) * s->ow <= kTileRows) return t;
+    return 0;
+}
+
 bool tc_conv3x3_fwd_supported(const b200cnn_conv_shape* s) {
-    return s->k == 3 && s->c == kCin && (s->oc == 16 || s->oc == 32 || s->oc == 64) && s->oh * s->ow <= kTileRows &&
-           s->stride >= 1 && s->stride <= 8 && (s->ow - 1) * s->stride + 1 <= 256 && (s->oh - 1) * s->stride + 1 <= 256;
+    return s->k == 3 && s->c == kCin && (s->oc == 16 || s->oc == 32 || s->oc == 64) && fwd_tiles(s) > 0 && s->stride >= 1 &&
+           s->stride <= 8 && (s->ow - 1) * s->stride + 1 <= 256 && (s->oh - 1) * s->stride + 1 <= 256;
 }
 
 // x: NHWC [n][h][w][16]; y: [n][ldy] with the sample's outputs CHW-flattened (ldy >= oc*oh*ow).
 int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s,
-                   int act, cudaStream_t st) {
+                   int act, cudaStream_t st, int nhwc_out) {
     if (!tc_conv3x3_fwd_supported(s)) return set_error(kInvalidValue, "tc_conv3x3_fwd: unsupported shape");
     const int pix = s->oh * s->ow;
-    const int group = kTileRows / pix;
+    const int tiles = fwd_tiles(s), oh_t = s->oh / tiles;
+    const int group = tiles > 1 ? 1 : kTileRows / pix;
     CUtensorMap tm;
     const uint64_t dims[4] = {uint64_t(s->c), uint64_t(s->w), uint64_t(s->h), uint64_t(s->n)};
     const uint64_t strides[4] = {0, uint64_t(s->c) * 4, uint64_t(s->w) * s->c * 4, uint64_t(s->h) * s->w * s->c * 4};
-    const uint32_t box[4] = {uint32_t(s->c), uint32_t((s->ow - 1) * s->stride + 1), uint32_t((s->oh - 1) * s->stride + 1),
+    const uint32_t box[4] = {uint32_t(s->c), uint32_t((s->ow - 1) * s->stride + 1), uint32_t((oh_t - 1) * s->stride + 1),
                              uint32_t(group)};
     const uint32_t estr[4] = {1, uint32_t(s->stride), uint32_t(s->stride), 1};
     if (int rc = encode_tmap_f32(&tm, x_nhwc, 4, dims, strides, box, estr, 64)) return rc;
@@ -427,7 +583,7 @@ int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y
         const char* v = getenv("B200CNN_TMA_STORE");
         return v && v[0] == '1';
     }();
-    if (tma_store && ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0 && size_t(group) * per_sample * 4 <= size_t(kTaps) * kTileRows * kCin * 4)
+    if (tma_store && !nhwc_out && tiles == 1 && ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0 && size_t(group) * per_sample * 4 <= size_t(kTaps) * kTileRows * kCin * 4)
         for (int c = 256; c >= 4; c -= 4)
             if (per_sample % c == 0) {
                 bw = c;
@@ -439,8 +595,8 @@ int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y
         const uint32_t ybox[2] = {uint32_t(bw), uint32_t(group)};
         if (int rc = encode_tmap_f32(&tmy, y, 2, ydims, ystr, ybox, nullptr, 0)) return rc;
     }
-    ConvFwdArgs a{w, b, y, ldy, s->n, s->oc, s->oh, s->ow, s->pad, group, act, bw};
-    const int grid = ceil_div(s->n, group);
+    ConvFwdArgs a{w, b, y, ldy, s->n, s->oc, s->oh, s->ow, s->pad, group, act, s->stride, bw, tiles, oh_t, nhwc_out};
+    const int grid = tiles > 1 ? s->n * tiles : ceil_div(s->n, group);
 #define B200CNN_LAUNCH_FWD(OCV)                                                                                   \
     do {                                                                                                          \
         auto kern = tc_conv3x3_fwd_kernel<OCV>;                                                                   \
@@ -487,6 +643,40 @@ int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const 
     }
     B200CNN_CUDA(launch_kernel(kern, dim3(ceil_div(s->n, group)), dim3(kConvThreads), smem, st, tm, a));
     B200CNN_CHECK_LAUNCH("tc_conv3x3s2_bwd_data");
+    return 0;
+}
+
+static int s1_tiles(const b200cnn_conv_shape* s) {
+    for (int t = 1; t <= s->h; t++)
+        if (s->h % t == 0 && (s->h / t) * s->w <= kTileRows) return t;
+    return 0;
+}
+
+bool tc_conv3x3s1_bwd_data_supported(const b200cnn_conv_shape* s) {
+    return s->k == 3 && s->stride == 1 && s->pad == 1 && s->c == 16 && s->oc == 32 && s->oh == s->h && s->ow == s->w && s->w <= 128 &&
+           s1_tiles(s) > 0;
+}
+
+// dz: NHWC [n][h][w][32]; a_prev / dx: NHWC [n][h][w][16].
+int tc_conv3x3s1_bwd_data(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
+                          const b200cnn_conv_shape* s, cudaStream_t st) {
+    if (!tc_conv3x3s1_bwd_data_supported(s)) return set_error(kInvalidValue, "tc_conv3x3s1_bwd_data: unsupported shape");
+    const int tiles = s1_tiles(s), h_t = s->h / tiles;
+    CUtensorMap tm;
+    const uint64_t dims[4] = {uint64_t(s->oc), uint64_t(s->ow), uint64_t(s->oh), uint64_t(s->n)};
+    const uint64_t strides[4] = {0, uint64_t(s->oc) * 4, uint64_t(s->ow) * s->oc * 4, uint64_t(s->oh) * s->ow * s->oc * 4};
+    const uint32_t box[4] = {uint32_t(s->oc), uint32_t(s->ow), uint32_t(h_t), 1};
+    if (int rc = encode_tmap_f32(&tm, dz_nhwc, 4, dims, strides, box, nullptr, 128)) return rc;
+    ConvS1BwdArgs a{w, a_prev_nhwc, dx_nhwc, s->n, s->h, s->w, tiles, h_t, act_prev};
+    auto kern = tc_conv3x3s1_bwd_data_kernel<32, 16>;
+    constexpr size_t smem = size_t(kTaps) * (kTileRows * 32 * 4 + 16 * 32 * 4) + 1024 + 64;
+    static bool configured = false;
+    if (!configured) {
+        B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        configured = true;
+    }
+    B200CNN_CUDA(launch_kernel(kern, dim3(s->n * tiles), dim3(kConvThreads), smem, st, tm, a));
+    B200CNN_CHECK_LAUNCH("tc_conv3x3s1_bwd_data");
     return 0;
 }
 

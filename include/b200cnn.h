@@ -84,6 +84,19 @@ int b200cnn_conv3x3_fwd_nhwc(const float* x_nhwc, const float* w, const float* b
  * or, with dz_is_chw, the CHW gradient an FC layer produces for its flattened input (gathered in-kernel). */
 int b200cnn_conv3x3s2_bwd_data_nhwc(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
                                     float* dx_nhwc, const b200cnn_conv_shape* s, b200cnn_stream stream);
+/* The same forward kernel with an NHWC output [n][oh][ow][oc] (the pooled topology: conv -> ReLU -> max-pool), images
+ * of more than 128 output pixels are cut into bands of whole rows (14x14 -> 2 x 7 rows). */
+int b200cnn_conv3x3_fwd_nhwc_to_nhwc(const float* x_nhwc, const float* w, const float* b, float* y_nhwc,
+                                     const b200cnn_conv_shape* s, int act, b200cnn_stream stream);
+/* 3x3 / stride 1 / pad 1, 32 -> 16 channels (cnn.c:235 for the pooled topology's second convolution): dz, a_prev, dx NHWC. */
+int b200cnn_conv3x3s1_bwd_data_nhwc(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
+                                    const b200cnn_conv_shape* s, b200cnn_stream stream);
+/* Max pooling on NHWC activations (K7): y NHWC or, with out_chw, CHW-flattened rows for a fully connected layer;
+ * backward takes dy NHWC or CHW-flattened (dy_chw) and multiplies by act'(a_prev) of the layer below. */
+int b200cnn_maxpool_nhwc_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride, int out_chw,
+                             b200cnn_stream stream);
+int b200cnn_maxpool_nhwc_bwd(const float* dy, int dy_chw, const int32_t* argmax, const float* a_prev, int act_prev, float* dx, int n,
+                             int c, int h, int w, int k, int stride, b200cnn_stream stream);
 /* dw (OIHW) / db for NHWC activations: x NHWC (or a 1-channel image, uint8 allowed), dz NHWC or CHW.
  * Register-tiled CUDA-core kernel + fixed-order reduction of per-block partial sums held in `scratch`
  * (zero the scratch once after allocating it: its first 128 bytes hold a self-resetting completion counter; the

@@ -130,6 +130,10 @@ def cuda():
     _sig(lib, "b200cnn_conv2d_bwd_weight_noalloc", i, vp, vp, i, vp, vp, i, cs, vp)
     _sig(lib, "b200cnn_conv3x3_fwd_nhwc", i, vp, vp, vp, vp, i, cs, i, vp)
     _sig(lib, "b200cnn_conv3x3s2_bwd_data_nhwc", i, vp, i, vp, vp, i, vp, cs, vp)
+    _sig(lib, "b200cnn_conv3x3_fwd_nhwc_to_nhwc", i, vp, vp, vp, vp, cs, i, vp)
+    _sig(lib, "b200cnn_conv3x3s1_bwd_data_nhwc", i, vp, vp, vp, i, vp, cs, vp)
+    _sig(lib, "b200cnn_maxpool_nhwc_fwd", i, vp, vp, vp, i, i, i, i, i, i, i, vp)
+    _sig(lib, "b200cnn_maxpool_nhwc_bwd", i, vp, i, vp, vp, i, vp, i, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes", sz, cs)
     _sig(lib, "b200cnn_conv2d_bwd_weight_nhwc", i, vp, i, vp, i, vp, vp, i, vp, cs, vp)
     _sig(lib, "b200cnn_linear_fwd", i, vp, vp, vp, vp, i, i, i, i, i, vp)

@@ -480,3 +480,93 @@ def test_fc_mid_kernel(shape):
         got = met.cpu().numpy()
         assert got[3] == m and abs(got[2] - float((rp.argmax(1) == lab.long()).sum())) <= 1
         assert got[0] == pytest.approx(float(-torch.log(rp[torch.arange(m), lab.long()]).sum()), rel=3e-3)
+
+
+@pytest.mark.parametrize("n", [1, 3, 64])
+@pytest.mark.parametrize("act", ["relu", "none"])
+def test_tcgen05_conv3x3_stride1_banded_nhwc_out(n, act):
+    """The pooled topology's second convolution (16 -> 32 channels at 14x14, stride 1): 196 output pixels per image are
+    cut into two 7-row bands of the tcgen05 implicit GEMM; output NHWC, then also the CHW-flattened form."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    torch.backends.cudnn.allow_tf32 = False
+    x = torch.randn(n, 16, 14, 14, device="cuda")
+    w, b = 0.2 * torch.randn(32, 16, 3, 3, device="cuda"), 0.1 * torch.randn(32, device="cuda")
+    want = F.conv2d(x, w, b, 1, 1)
+    if act == "relu":
+        want = torch.relu(want)
+    shp = N.ConvShape(n, 16, 14, 14, 32, 14, 14, 3, 1, 1)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    code = N.ACT_RELU if act == "relu" else N.ACT_NONE
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    y = torch.full((n, 14, 14, 32), 7.0, device="cuda")
+    N.check(lib.b200cnn_conv3x3_fwd_nhwc_to_nhwc(p(xn), p(w), p(b), p(y), C.byref(shp), code, st), "conv3x3_fwd_nhwc_to_nhwc")
+    torch.cuda.synchronize()
+    _close(y.permute(0, 3, 1, 2), want, 4e-3)
+    ldy = 32 * 196
+    y2 = torch.full((n, ldy), 7.0, device="cuda")
+    N.check(lib.b200cnn_conv3x3_fwd_nhwc(p(xn), p(w), p(b), p(y2), ldy, C.byref(shp), code, st), "conv3x3_fwd_nhwc")
+    torch.cuda.synchronize()
+    _close(y2.reshape(n, 32, 14, 14), want, 4e-3)
+
+
+@pytest.mark.parametrize("n", [1, 3, 64])
+@pytest.mark.parametrize("mask", [True, False])
+def test_tcgen05_conv3x3_stride1_backward_data(n, mask):
+    """b200cnn_conv3x3s1_bwd_data_nhwc (32 -> 16 channels at 14x14, stride 1) against conv_transpose2d in fp32."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    torch.backends.cudnn.allow_tf32 = False
+    dz = torch.randn(n, 32, 14, 14, device="cuda")
+    w = 0.2 * torch.randn(32, 16, 3, 3, device="cuda")
+    a_prev = torch.relu(torch.randn(n, 16, 14, 14, device="cuda"))
+    want = F.conv_transpose2d(dz, w, None, 1, 1)
+    if mask:
+        want = want * (a_prev > 0)
+    dx = torch.full((n, 14, 14, 16), 7.0, device="cuda")
+    shp = N.ConvShape(n, 16, 14, 14, 32, 14, 14, 3, 1, 1)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    ap = a_prev.permute(0, 2, 3, 1).contiguous()
+    N.check(lib.b200cnn_conv3x3s1_bwd_data_nhwc(p(dz.permute(0, 2, 3, 1).contiguous()), p(w), p(ap) if mask else None,
+                                                N.ACT_RELU if mask else N.ACT_NONE, p(dx), C.byref(shp), st), "conv3x3s1_bwd_data_nhwc")
+    torch.cuda.synchronize()
+    _close(dx.permute(0, 3, 1, 2), want, 4e-3)
+
+
+@pytest.mark.parametrize("shape", [(5, 16, 28, 28), (3, 32, 14, 14)])
+@pytest.mark.parametrize("chw", [0, 1])
+def test_maxpool_nhwc_forward_backward(shape, chw):
+    """NHWC max pooling (2x2 / stride 2): NHWC or CHW-flattened output / incoming gradient, ReLU mask of the layer below."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    n, c, h, w = shape
+    x = torch.relu(torch.randn(n, c, h, w, device="cuda")).requires_grad_(True)
+    ref = F.max_pool2d(x, 2, 2)
+    dy = torch.randn_like(ref)
+    ref.backward(dy)
+    want_dx = x.grad * (x > 0)
+    xn = x.detach().permute(0, 2, 3, 1).contiguous()
+    oh, ow = h // 2, w // 2
+    y = torch.empty(n * c * oh * ow, device="cuda")
+    arg = torch.empty(n * oh * ow * c, dtype=torch.int32, device="cuda")
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    N.check(lib.b200cnn_maxpool_nhwc_fwd(p(xn), p(y), p(arg), n, c, h, w, 2, 2, chw, st), "maxpool_nhwc_fwd")
+    got = y.reshape(n, c, oh, ow) if chw else y.reshape(n, oh, ow, c).permute(0, 3, 1, 2)
+    assert torch.equal(got, ref.detach())
+    dyl = dy.contiguous() if chw else dy.permute(0, 2, 3, 1).contiguous()
+    dx = torch.empty(n, h, w, c, device="cuda")
+    N.check(lib.b200cnn_maxpool_nhwc_bwd(p(dyl), chw, p(arg), p(xn), N.ACT_RELU, p(dx), n, c, h, w, 2, 2, st), "maxpool_nhwc_bwd")
+    torch.cuda.synchronize()
+    assert float((dx.permute(0, 3, 1, 2) - want_dx).abs().max()) < 1e-6
