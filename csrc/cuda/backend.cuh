@@ -86,6 +86,7 @@ int tc_conv1_bwd_weight(const uint8_t* x, const float* dz_nhwc, float* dw, float
 // conv_nhwc.cu / conv.cu
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
 int nhwc_bwd_weight_chunks(int n, int* spb_out);
+size_t nhwc_bwd_weight_smem_bytes(const b200cnn_conv_shape* s);
 int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
                          float* partials, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st,
                          float* sgd_w = nullptr, float* sgd_b = nullptr, const float* lr_dev = nullptr,

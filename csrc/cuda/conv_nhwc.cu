@@ -298,6 +298,17 @@ bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8) {
     return !x_is_u8 && s->c % 4 == 0 && s->oc % 4 == 0 && (s->oc / 4) * (s->c / 4) * s->k * s->k <= 512;
 }
 
+int nhwc_bwd_weight_chunks(int n, int* spb_out);
+
+// Dynamic shared memory of the CUDA-core weight-gradient kernels for a batch of s->n samples (every sample of a block is
+// staged at once); a shape is usable only while this stays under the 200 KB the launcher allows.
+size_t nhwc_bwd_weight_smem_bytes(const b200cnn_conv_shape* s) {
+    int spb = 1;
+    nhwc_bwd_weight_chunks(s->n, &spb);
+    const size_t in_floats = s->c == 1 ? size_t((s->h * s->w + 3) & ~3) : size_t(s->h) * s->w * s->c;
+    return size_t(spb) * (in_floats + size_t(s->oh) * s->ow * s->oc) * sizeof(float) + (s->c == 1 ? 2 * kC1Threads * sizeof(float) : 0);
+}
+
 // Blocks (= partial sums) used for a batch of n samples.
 int nhwc_bwd_weight_chunks(int n, int* spb_out) {
     int spb = ceil_div(n, 148);

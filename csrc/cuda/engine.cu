@@ -91,6 +91,8 @@ struct b200cnn_engine {
     int wait_layer = 1;       // data parallel: first layer whose parameters a deferred (two-shot push) update may write
     bool last_fast = false;   // layout of layer 1's activations in the last forward (NHWC when true)
     bool fast_chain = false;  // conv(C_in=1) -> tc conv3x3 -> FC pattern: NHWC activations + tcgen05 convolutions
+    bool pool_chain = false;  // conv(C_in=1) -> pool -> tc conv3x3 (stride 1) -> pool -> FC: the same, all NHWC up to the last pool
+    unsigned nhwc_mask = 0;   // bit li: layer li's activations of the last forward are NHWC on the device
 };
 
 namespace {
@@ -116,6 +118,7 @@ b200cnn_conv_shape conv_shape(const EngineLayer& prev, const EngineLayer& l, int
 // The tensor-core convolution chain is used when the topology allows it and the backend is not pinned
 // to the CUDA-core kernels.
 bool use_fast_chain(const b200cnn_engine* e) { return e->fast_chain && current_backend() != B200CNN_BACKEND_SIMT; }
+bool use_pool_chain(const b200cnn_engine* e) { return e->pool_chain && current_backend() != B200CNN_BACKEND_SIMT; }
 
 // True when the last three layers are FC(tanh) -> FC(tanh) -> FC(softmax) of sizes the fused head kernel takes.
 bool use_head(const b200cnn_engine* e, int batch) {
@@ -162,7 +165,9 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
                     cudaStream_t st, int* launches, size_t stop = ~size_t(0)) {
     auto& L = e->layers;
     const bool fast = use_fast_chain(e);
+    const bool poolc = use_pool_chain(e);
     e->last_fast = fast;
+    e->nhwc_mask = fast ? 2u : poolc ? 14u : 0u;  // NHWC layers: 1, or 1-3 (the second pool writes CHW rows for the FC layer)
     for (size_t li = 1; li < L.size() && li < stop; li++) {
         EngineLayer& l = L[li];
         const EngineLayer& p = L[li - 1];
@@ -176,8 +181,10 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
         switch (l.d.type) {
             case B200CNN_LAYER_CONV: {
                 const b200cnn_conv_shape s = conv_shape(p, l, batch);
-                if (fast && li == 1)  // first conv: CUDA cores (1 input channel), NHWC output for the TMA loads below
+                if ((fast || poolc) && li == 1)  // first conv: CUDA cores (1 input channel), NHWC output for the TMA loads below
                     rc = simt_conv2d_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, l.a, &s, l.act, 1, st);
+                else if (poolc && li == 3)  // 196 pixels per image: two bands of the implicit GEMM, NHWC output for the pool
+                    rc = tc_conv3x3_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a, 0, &s, l.act, st, 1);
                 else if (fast && li == 2)  // implicit GEMM on tcgen05, output CHW-flattened for the FC layer
                     rc = tc_conv3x3_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a, l.ld, &s,
                                         l.act, st);
@@ -187,6 +194,10 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
             }
             case B200CNN_LAYER_POOL:
                 if (in_u8) return set_error(kInvalidValue, "engine: a pool layer cannot read uint8 input directly");
+                if (poolc)  // NHWC in; NHWC out, except the last pool, whose output an FC layer reads as CHW rows
+                    rc = maxpool_nhwc_fwd(static_cast<const float*>(in), l.a, l.argmax, batch, p.d.depth, p.d.height, p.d.width, l.d.k,
+                                          l.d.stride, li == 4 ? 1 : 0, st);
+                else
                 rc = b200cnn_maxpool_fwd(static_cast<const float*>(in), l.a, l.argmax, batch, p.d.depth, p.d.height,
                                          p.d.width, l.d.k, l.d.stride, st);
                 break;
@@ -267,6 +278,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
     auto& L = e->layers;
     float* grads = cur_grads(e);
     const bool fast = use_fast_chain(e);
+    const bool poolc = use_pool_chain(e);
     cudaStream_t side = e->side;
     e->bucket_lo = e->bucket_hi = -1;
     e->tail_lo = e->tail_hi = -1;
@@ -292,6 +304,10 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
         int rc = 0;
         if (l.d.type == B200CNN_LAYER_POOL) {
             if (li > 1) {
+                if (poolc)  // gradient arrives CHW (from the FC layer) at the last pool, NHWC elsewhere; leaves NHWC
+                    rc = maxpool_nhwc_bwd(l.dz, li == 4 ? 1 : 0, l.argmax, p.a, p.act, p.dz, batch, p.d.depth, p.d.height, p.d.width,
+                                          l.d.k, l.d.stride, st);
+                else
                 rc = b200cnn_maxpool_bwd(l.dz, l.argmax, p.a, p.act, p.dz, batch, p.d.depth, p.d.height, p.d.width, l.d.k,
                                          l.d.stride, st);
                 if (rc) return rc;
@@ -317,10 +333,11 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             if (launches) (*launches)++;
         } else {
             const b200cnn_conv_shape s = conv_shape(p, l, batch);
-            if (fast && li <= 2) {
+            const bool nhwc_path = (fast && li <= 2) || (poolc && (li == 1 || li == 3));
+            if (nhwc_path) {
                 const bool fuse = fuse_update && li == 1;  // single GPU: this kernel's last block also applies the update
                 const bool xc = fused_tail && li == 1;  // this kernel exchanges its result with the peers itself
-                rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/li == 2, grads + l.w_off, grads + l.b_off, 0,
+                rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/fast && li == 2, grads + l.w_off, grads + l.b_off, 0,
                                           li == 1 ? e->scratch1 : e->scratch, reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, ws,
                                           fuse ? e->params + l.w_off : nullptr, fuse ? e->params + l.b_off : nullptr, e->lr_dev,
                                           xc ? &xchg : nullptr, long(l.w_off), long(l.b_off));
@@ -331,7 +348,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
                 rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0,
                                               li == 1 ? e->scratch1 : e->scratch, &s, ws);
             // (the single-channel kernel reduces in its last block: one launch; every other path is kernel + reduce)
-            if (launches) (*launches) += (fast && li <= 2 && p.d.depth == 1) ? 1 : 2;
+            if (launches) (*launches) += (nhwc_path && p.d.depth == 1) ? 1 : 2;
         }
         if (rc) return rc;
 
@@ -344,6 +361,8 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
                 const b200cnn_conv_shape s = conv_shape(p, l, batch);
                 if (fast && li == 2)
                     rc = tc_conv3x3s2_bwd_data(l.dz, /*dz_is_chw=*/1, e->params + l.w_off, p.a, p.act, p.dz, &s, st);
+                else if (poolc && li == 3)  // the layer below is a pool: no activation derivative to apply
+                    rc = tc_conv3x3s1_bwd_data(l.dz, e->params + l.w_off, nullptr, B200CNN_ACT_NONE, p.dz, &s, st);
                 else
                     rc = b200cnn_conv2d_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, &s, st);
             }
@@ -504,6 +523,24 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
             size_t chunks = 0;  // worst case over every legal batch (same non-monotonic shape as above, period 148)
             for (int n = 1; n <= max_batch; n++) chunks = std::max(chunks, size_t(nhwc_bwd_weight_chunks(n, nullptr)));
             scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[2].nw + e->layers[2].nb) * sizeof(float) + 128);
+            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float) + 128);
+        }
+    }
+    // The pooled variant conv -> pool -> conv -> pool -> FC: first convolution on the CUDA cores (one input channel),
+    // the second one (stride 1, 14x14) as a banded implicit GEMM on tcgen05, NHWC between them.
+    if (nlayers >= 6 && e->layers[0].d.depth == 1 && e->layers[1].d.type == B200CNN_LAYER_CONV &&
+        e->layers[2].d.type == B200CNN_LAYER_POOL && e->layers[3].d.type == B200CNN_LAYER_CONV &&
+        e->layers[4].d.type == B200CNN_LAYER_POOL && e->layers[5].d.type == B200CNN_LAYER_FULL) {
+        const b200cnn_conv_shape s1 = conv_shape(e->layers[0], e->layers[1], max_batch);
+        const b200cnn_conv_shape s3 = conv_shape(e->layers[2], e->layers[3], max_batch);
+        constexpr size_t kSmemLimit = 200 * 1024;
+        e->pool_chain = s1.oc % 16 == 0 && tc_conv3x3_fwd_supported(&s3) && tc_conv3x3s1_bwd_data_supported(&s3) &&
+                        nhwc_bwd_weight_supported(&s1, 1) && nhwc_bwd_weight_supported(&s3, 0) &&
+                        nhwc_bwd_weight_smem_bytes(&s1) <= kSmemLimit && nhwc_bwd_weight_smem_bytes(&s3) <= kSmemLimit;
+        if (e->pool_chain) {
+            size_t chunks = 0;
+            for (int n = 1; n <= max_batch; n++) chunks = std::max(chunks, size_t(nhwc_bwd_weight_chunks(n, nullptr)));
+            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[3].nw + e->layers[3].nb) * sizeof(float) + 128);
             scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float) + 128);
         }
     }
@@ -847,7 +884,7 @@ extern "C" int b200cnn_engine_layer_output(b200cnn_engine* e, int layer, int bat
     const EngineLayer& l = e->layers[size_t(layer)];
     B200CNN_CUDA(cudaMemcpy2D(host, l.nnodes * sizeof(float), l.a, l.ld * sizeof(float), l.nnodes * sizeof(float),
                               size_t(batch), cudaMemcpyDeviceToHost));
-    if (e->last_fast && layer == 1) {
+    if ((e->nhwc_mask >> layer) & 1u) {
         // The tensor-core chain keeps this layer NHWC on the device; callers always get CHW.
         const int c = l.d.depth, hw = l.d.width * l.d.height;
         std::vector<float> tmp(size_t(l.nnodes));
@@ -862,6 +899,9 @@ extern "C" int b200cnn_engine_layer_output(b200cnn_engine* e, int layer, int bat
 }
 
 extern "C" int b200cnn_engine_launches_per_step(const b200cnn_engine* e) { return e->launches_per_step; }
+extern "C" int b200cnn_engine_conv_path(const b200cnn_engine* e) {
+    return use_fast_chain(e) ? B200CNN_CONV_PATH_TC : use_pool_chain(e) ? B200CNN_CONV_PATH_TC_POOL : B200CNN_CONV_PATH_GENERIC;
+}
 
 // Data-parallel hook (declared in comm.cuh): the communicator must have been created over this
 // engine's bound parameter / gradient buffers.

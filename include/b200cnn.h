@@ -249,6 +249,12 @@ int b200cnn_engine_reset_metrics(b200cnn_engine* e, b200cnn_stream stream);
 int b200cnn_engine_layer_output(b200cnn_engine* e, int layer, int batch, float* host);
 /* Number of kernels one train_step launches (for launch accounting in benchmarks). */
 int b200cnn_engine_launches_per_step(const b200cnn_engine* e);
+/* Which convolution kernels the engine runs under the current backend setting: the generic CHW kernels on the CUDA
+ * cores, the NHWC chain with tcgen05 implicit GEMMs (reference topology), or the same for conv -> pool -> conv -> pool. */
+#define B200CNN_CONV_PATH_GENERIC 0
+#define B200CNN_CONV_PATH_TC 1
+#define B200CNN_CONV_PATH_TC_POOL 2
+int b200cnn_engine_conv_path(const b200cnn_engine* e);
 
 #ifdef __cplusplus
 }

@@ -171,6 +171,7 @@ def cuda():
     _sig(lib, "b200cnn_engine_reset_metrics", i, vp, vp)
     _sig(lib, "b200cnn_engine_layer_output", i, vp, i, i, c_float_p)
     _sig(lib, "b200cnn_engine_launches_per_step", i, vp)
+    _sig(lib, "b200cnn_engine_conv_path", i, vp)
     _sig(lib, "b200cnn_engine_attach_comm", i, vp, vp)
     # comm
     _sig(lib, "b200cnn_comm_region_bytes", sz, sz)

@@ -177,6 +177,12 @@ class Engine:
     def launches_per_step(self):
         return self.lib.b200cnn_engine_launches_per_step(self.handle)
 
+    @property
+    def conv_path(self):
+        """'generic' (CHW kernels on the CUDA cores), 'tcgen05' (NHWC chain, reference topology) or 'tcgen05_pool'
+        (the same for conv -> pool -> conv -> pool) under the current backend setting."""
+        return ("generic", "tcgen05", "tcgen05_pool")[self.lib.b200cnn_engine_conv_path(self.handle)]
+
     # ---- results ------------------------------------------------------------------------------
     def metrics_tensor(self):
         """Device tensor view [4] = {sum CE, sum MSE, #correct, #samples} since the last reset."""

@@ -2,7 +2,7 @@
 
 Runs the graph-captured step under torch.profiler (Kineto/CUPTI records the kernels our .so launches too), takes
 the kernels of one step in the middle of the run and prints start offset, duration, stream and the gap to the
-previous kernel on the same stream.  Usage: python tools/timeline.py [batch] [steps]
+previous kernel on the same stream.  Usage: python tools/timeline.py [batch] [steps] [--pool] [--simt]
 """
 import os
 import sys
@@ -14,8 +14,12 @@ from torch.profiler import ProfilerActivity, profile
 from mpi_cuda_cnn_b200.engine import Engine
 from mpi_cuda_cnn_b200.ops import functional as F200
 
-B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
-STEPS = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+POOL, SIMT = "--pool" in sys.argv, "--simt" in sys.argv
+_pos = [a for a in sys.argv[1:] if not a.startswith("--")]
+B = int(_pos[0]) if len(_pos) > 0 else 256
+STEPS = int(_pos[1]) if len(_pos) > 1 else 40
+if SIMT:
+    F200.set_backend("simt")
 WORLD = int(os.environ.get("WORLD_SIZE", "1"))
 RANK = int(os.environ.get("RANK", "0"))
 dev = torch.device("cuda:0")
@@ -33,7 +37,8 @@ elif os.environ.get("B200CNN_BENCH_FORCE_DP") == "1":  # the data-parallel launc
     _tr = DataParallelTrainer(0, 1, dev, batch=B, mode="fused")
     eng = _tr.engine
 else:
-    eng = Engine(max_batch=B, device=dev)
+    from mpi_cuda_cnn_b200 import mnist_layers, pool_layers
+    eng = Engine(pool_layers() if POOL else mnist_layers(), max_batch=B, device=dev)
     eng.init_params(seed=1)
 x, y = F200.synthetic_batch(B * 8, seed=1, device=dev)
 xs = [x[i * B:(i + 1) * B].contiguous() for i in range(8)]
