@@ -86,11 +86,20 @@ int tc_conv1_bwd_weight(const uint8_t* x, const float* dz_nhwc, float* dw, float
 // conv_nhwc.cu / conv.cu
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
 int nhwc_bwd_weight_chunks(int n, int* spb_out);
+int nhwc_bwd_weight_chunks_for(const b200cnn_conv_shape* s, int* spb_out);
 size_t nhwc_bwd_weight_smem_bytes(const b200cnn_conv_shape* s);
 int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
                          float* partials, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st,
                          float* sgd_w = nullptr, float* sgd_b = nullptr, const float* lr_dev = nullptr,
                          const TailXchg* xchg = nullptr, long w_off = 0, long b_off = 0);
+// fused first layer of the pooled topology: conv (1 channel, 3x3 / s1 / p1) + activation + 2x2 max pool, and its weight
+// gradient straight from the pooled gradient
+bool conv1_pool_supported(const b200cnn_conv_shape* s, int pool_k, int pool_stride);
+int conv1_pool_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* a_full, float* yp, int32_t* argmax,
+                   const b200cnn_conv_shape* s, int act, cudaStream_t st);
+int conv1_pool_bwd_weight(const void* x, int x_is_u8, const float* dyp, const float* yp, const int32_t* argmax, int act, float* dw,
+                          float* db, int accumulate, float* partials, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st,
+                          float* sgd_w = nullptr, float* sgd_b = nullptr, const float* lr_dev = nullptr);
 int simt_conv2d_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* y, const b200cnn_conv_shape* s,
                     int act, int nhwc_out, cudaStream_t st);
 int reduce_conv_partials(const float* partials, float* dw, float* db, int chunks, int nw, int nb, int accumulate,

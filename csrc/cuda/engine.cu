@@ -93,6 +93,9 @@ struct b200cnn_engine {
     bool fast_chain = false;  // conv(C_in=1) -> tc conv3x3 -> FC pattern: NHWC activations + tcgen05 convolutions
     bool pool_chain = false;  // conv(C_in=1) -> pool -> tc conv3x3 (stride 1) -> pool -> FC: the same, all NHWC up to the last pool
     unsigned nhwc_mask = 0;   // bit li: layer li's activations of the last forward are NHWC on the device
+    bool pool_fused = false;  // pool chain: conv1 + ReLU + pool as one kernel, conv1's weight gradient from the pooled gradient
+    bool keep_full = true;    // ... and whether that kernel also stores the un-pooled activations (forward(): yes, steps: no)
+    bool l1_stale = false;    // the last forward did not store layer 1's activations
 };
 
 namespace {
@@ -168,6 +171,8 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
     const bool poolc = use_pool_chain(e);
     e->last_fast = fast;
     e->nhwc_mask = fast ? 2u : poolc ? 14u : 0u;  // NHWC layers: 1, or 1-3 (the second pool writes CHW rows for the FC layer)
+    const bool fusedp = poolc && e->pool_fused;
+    e->l1_stale = fusedp && !e->keep_full;
     for (size_t li = 1; li < L.size() && li < stop; li++) {
         EngineLayer& l = L[li];
         const EngineLayer& p = L[li - 1];
@@ -181,7 +186,10 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
         switch (l.d.type) {
             case B200CNN_LAYER_CONV: {
                 const b200cnn_conv_shape s = conv_shape(p, l, batch);
-                if ((fast || poolc) && li == 1)  // first conv: CUDA cores (1 input channel), NHWC output for the TMA loads below
+                if (fusedp && li == 1)  // convolution + ReLU + the pool above it in one kernel (layer 2 is skipped below)
+                    rc = conv1_pool_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, e->keep_full ? l.a : nullptr, L[2].a,
+                                        L[2].argmax, &s, l.act, st);
+                else if ((fast || poolc) && li == 1)  // first conv: CUDA cores (1 input channel), NHWC output for the TMA loads below
                     rc = simt_conv2d_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, l.a, &s, l.act, 1, st);
                 else if (poolc && li == 3)  // 196 pixels per image: two bands of the implicit GEMM, NHWC output for the pool
                     rc = tc_conv3x3_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a, 0, &s, l.act, st, 1);
@@ -194,6 +202,7 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
             }
             case B200CNN_LAYER_POOL:
                 if (in_u8) return set_error(kInvalidValue, "engine: a pool layer cannot read uint8 input directly");
+                if (fusedp && li == 2) continue;  // computed by the first convolution's kernel
                 if (poolc)  // NHWC in; NHWC out, except the last pool, whose output an FC layer reads as CHW rows
                     rc = maxpool_nhwc_fwd(static_cast<const float*>(in), l.a, l.argmax, batch, p.d.depth, p.d.height, p.d.width, l.d.k,
                                           l.d.stride, li == 4 ? 1 : 0, st);
@@ -279,6 +288,8 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
     float* grads = cur_grads(e);
     const bool fast = use_fast_chain(e);
     const bool poolc = use_pool_chain(e);
+    const bool fusedp = poolc && e->pool_fused;
+    const size_t second = poolc ? 3 : 2;  // the first parameterised layer above layer 1
     cudaStream_t side = e->side;
     e->bucket_lo = e->bucket_hi = -1;
     e->tail_lo = e->tail_hi = -1;
@@ -303,6 +314,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
         const int in_u8 = (li == 1) ? is_u8 : 0;
         int rc = 0;
         if (l.d.type == B200CNN_LAYER_POOL) {
+            if (fusedp && li == 2) continue;  // the first convolution takes its weight gradient from THIS layer's gradient
             if (li > 1) {
                 if (poolc)  // gradient arrives CHW (from the FC layer) at the last pool, NHWC elsewhere; leaves NHWC
                     rc = maxpool_nhwc_bwd(l.dz, li == 4 ? 1 : 0, l.argmax, p.a, p.act, p.dz, batch, p.d.depth, p.d.height, p.d.width,
@@ -334,8 +346,12 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
         } else {
             const b200cnn_conv_shape s = conv_shape(p, l, batch);
             const bool nhwc_path = (fast && li <= 2) || (poolc && (li == 1 || li == 3));
-            if (nhwc_path) {
-                const bool fuse = fuse_update && li == 1;  // single GPU: this kernel's last block also applies the update
+            const bool fuse = fuse_update && li == 1;  // single GPU: this kernel's last block also applies the update
+            if (fusedp && li == 1) {
+                rc = conv1_pool_bwd_weight(in, in_u8, L[2].dz, L[2].a, L[2].argmax, l.act, grads + l.w_off, grads + l.b_off, 0, e->scratch1,
+                                           reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, ws, fuse ? e->params + l.w_off : nullptr,
+                                           fuse ? e->params + l.b_off : nullptr, e->lr_dev);
+            } else if (nhwc_path) {
                 const bool xc = fused_tail && li == 1;  // this kernel exchanges its result with the peers itself
                 rc = nhwc_conv_bwd_weight(in, in_u8, l.dz, /*dz_chw=*/fast && li == 2, grads + l.w_off, grads + l.b_off, 0,
                                           li == 1 ? e->scratch1 : e->scratch, reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, ws,
@@ -369,7 +385,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             if (rc) return rc;
             if (launches) (*launches)++;
         }
-        if (fuse_update && li == 2) {
+        if (fuse_update && li == second) {
             // Every layer above the first has its gradient (side stream) and nothing reads its weights any more once
             // this layer's data-gradient kernel (just issued on `st`) is done: update them now, next to the tail.
             B200CNN_CUDA(cudaEventRecord(e->ev_data, st));
@@ -443,7 +459,9 @@ int enqueue_sgd_range(b200cnn_engine* e, size_t begin, size_t end, cudaStream_t 
 
 // True when backward can apply the update itself (single GPU, tensor-core conv chain): layers >= 2 on the side
 // stream as soon as their weights are no longer read, layer 1 inside its weight-gradient kernel.
-bool can_fuse_update(const b200cnn_engine* e) { return !e->comm && use_fast_chain(e) && e->layers[2].nw > 0; }
+bool can_fuse_update(const b200cnn_engine* e) {
+    return !e->comm && ((use_fast_chain(e) && e->layers[2].nw > 0) || (use_pool_chain(e) && e->layers[3].nw > 0));
+}
 
 int enqueue_update(b200cnn_engine* e, cudaStream_t st, int* launches) {
     if (e->comm) return comm_join(e->comm, st);  // per-layer fused updates already enqueued
@@ -538,10 +556,20 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
                         nhwc_bwd_weight_supported(&s1, 1) && nhwc_bwd_weight_supported(&s3, 0) &&
                         nhwc_bwd_weight_smem_bytes(&s1) <= kSmemLimit && nhwc_bwd_weight_smem_bytes(&s3) <= kSmemLimit;
         if (e->pool_chain) {
-            size_t chunks = 0;
-            for (int n = 1; n <= max_batch; n++) chunks = std::max(chunks, size_t(nhwc_bwd_weight_chunks(n, nullptr)));
-            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[3].nw + e->layers[3].nb) * sizeof(float) + 128);
+            size_t chunks = 0, chunks3 = 0;
+            b200cnn_conv_shape t3 = s3;
+            for (int n = 1; n <= max_batch; n++) {
+                t3.n = n;
+                chunks = std::max(chunks, size_t(nhwc_bwd_weight_chunks(n, nullptr)));
+                chunks3 = std::max(chunks3, size_t(nhwc_bwd_weight_chunks_for(&t3, nullptr)));
+            }
+            scratch_bytes = std::max(scratch_bytes, chunks3 * size_t(e->layers[3].nw + e->layers[3].nb) * sizeof(float) + 128);
             scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float) + 128);
+            static const bool fuse_env = [] {
+                const char* v = getenv("B200CNN_POOL_FUSED");  // B200CNN_POOL_FUSED=0: separate conv / pool kernels (A/B timing)
+                return !(v && v[0] == '0');
+            }();
+            e->pool_fused = fuse_env && e->layers[1].act == B200CNN_ACT_RELU && conv1_pool_supported(&s1, e->layers[2].d.k, e->layers[2].d.stride);
         }
     }
     e->scratch_bytes = round_up(scratch_bytes, 512);
@@ -685,6 +713,7 @@ extern "C" int b200cnn_engine_forward(b200cnn_engine* e, const void* images, int
     e->last_batch = batch;
     if (e->comm)  // the peers' shards of the last update must have landed before anything reads the parameters
         if (int rc = b200cnn_comm_wait_weights(e->comm, stream)) return rc;
+    e->keep_full = true;  // a caller of forward() may look at every layer
     return enqueue_forward(e, images, x_is_u8, labels, batch, as_stream(stream), nullptr);
 }
 
@@ -712,6 +741,7 @@ static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const 
     const bool chain = use_chain(e, batch);
     const bool mid = !chain && use_mid(e, batch);
     const bool head = !chain && (mid || use_head(e, batch));
+    e->keep_full = false;  // a training step needs only the pooled activations of a fused conv + pool layer
     if (e->comm)
         if (int rc = comm_begin_step(e->comm, st)) return rc;
     if (chain) {
@@ -882,6 +912,8 @@ extern "C" int b200cnn_engine_layer_output(b200cnn_engine* e, int layer, int bat
     if (layer < 1 || layer >= int(e->layers.size()) || batch < 1 || batch > e->max_batch)
         return set_error(kInvalidValue, "engine_layer_output: bad layer / batch");
     const EngineLayer& l = e->layers[size_t(layer)];
+    if (layer == 1 && e->l1_stale)
+        return set_error(kInvalidValue, "engine_layer_output: a training step does not store the un-pooled activations of the fused conv + pool layer; call forward()");
     B200CNN_CUDA(cudaMemcpy2D(host, l.nnodes * sizeof(float), l.a, l.ld * sizeof(float), l.nnodes * sizeof(float),
                               size_t(batch), cudaMemcpyDeviceToHost));
     if ((e->nhwc_mask >> layer) & 1u) {

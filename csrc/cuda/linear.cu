@@ -92,7 +92,19 @@ extern "C" int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const 
     if (!s || !scratch || !nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "conv2d_bwd_weight_nhwc: unsupported shape or missing scratch");
     return nhwc_conv_bwd_weight(x, x_is_u8, dz, dz_is_chw, dw, db, accumulate, static_cast<float*>(scratch), nullptr, s, as_stream(stream));
 }
+extern "C" int b200cnn_conv1_pool_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* a_full, float* yp,
+                                      int32_t* argmax, const b200cnn_conv_shape* s, int act, b200cnn_stream stream) {
+    if (!s || !x || !w || !b || !yp || !argmax) return set_error(kInvalidValue, "conv1_pool_fwd: null argument");
+    return conv1_pool_fwd(x, x_is_u8, w, b, a_full, yp, argmax, s, act, as_stream(stream));
+}
+extern "C" int b200cnn_conv1_pool_bwd_weight(const void* x, int x_is_u8, const float* dyp, const float* yp, const int32_t* argmax,
+                                             int act, float* dw, float* db, int accumulate, void* scratch,
+                                             const b200cnn_conv_shape* s, b200cnn_stream stream) {
+    if (!s || !scratch || !x || !dyp || !yp || !argmax) return set_error(kInvalidValue, "conv1_pool_bwd_weight: null argument");
+    return conv1_pool_bwd_weight(x, x_is_u8, dyp, yp, argmax, act, dw, db, accumulate, static_cast<float*>(scratch), nullptr, s,
+                                 as_stream(stream));
+}
 extern "C" size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s) {
     // + 128 bytes: completion counter of the single-channel kernel (must be zero before the first use)
-    return size_t(nhwc_bwd_weight_chunks(s->n, nullptr)) * (size_t(s->oc) * s->c * s->k * s->k + s->oc) * sizeof(float) + 128;
+    return size_t(nhwc_bwd_weight_chunks_for(s, nullptr)) * (size_t(s->oc) * s->c * s->k * s->k + s->oc) * sizeof(float) + 128;
 }

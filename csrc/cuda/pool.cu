@@ -122,12 +122,113 @@ __global__ void maxpool_nhwc_bwd_kernel(const float* __restrict__ dy, int dy_chw
     dx[i] = g;
 }
 
+// One block per sample, for the pool in front of a fully connected layer: the winners are computed in NHWC order
+// (coalesced reads, coalesced argmax stores) into shared memory laid out CHW, then the sample's row leaves in one
+// coalesced sweep instead of 4-byte stores c*oh*ow floats apart.
+__global__ void maxpool_nhwc_fwd_chw_kernel(const float* __restrict__ x, float* __restrict__ y, int32_t* __restrict__ argmax,
+                                            int c, int h, int w, int oh, int ow, int k, int stride) {
+    extern __shared__ float sy[];  // [c][oh * ow]
+    pdl_wait();
+    pdl_launch_dependents();
+    const int s = blockIdx.x, per = oh * ow * c, opix = oh * ow;
+    const float* xs = x + size_t(s) * h * w * c;
+    for (int i = threadIdx.x; i < per; i += blockDim.x) {
+        const int ch = i % c, ox = (i / c) % ow, oy = i / (c * ow);
+        int best = -1;
+        float bv = 0.0f;
+        if (k == 2) {  // the four loads in flight together (the kernel is a chain of L2 round trips otherwise)
+            const int i00 = oy * stride * w + ox * stride;
+            const float v0 = __ldg(xs + size_t(i00) * c + ch), v1 = __ldg(xs + size_t(i00 + 1) * c + ch);
+            const float v2 = __ldg(xs + size_t(i00 + w) * c + ch), v3 = __ldg(xs + size_t(i00 + w + 1) * c + ch);
+            best = i00, bv = v0;
+            if (bv < v1) best = i00 + 1, bv = v1;
+            if (bv < v2) best = i00 + w, bv = v2;
+            if (bv < v3) best = i00 + w + 1, bv = v3;
+        } else {
+            for (int dy = 0; dy < k; dy++)
+                for (int dx = 0; dx < k; dx++) {
+                    const int idx = (oy * stride + dy) * w + ox * stride + dx;
+                    const float v = __ldg(xs + size_t(idx) * c + ch);
+                    if (best < 0 || bv < v) {
+                        best = idx;
+                        bv = v;
+                    }
+                }
+        }
+        sy[ch * opix + oy * ow + ox] = bv;
+        argmax[size_t(s) * per + i] = best;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < per; i += blockDim.x) y[size_t(s) * per + i] = sy[i];
+}
+
+// Scatter form of the backward pass for non-overlapping windows that tile the input exactly (k == stride, h = oh * k,
+// w = ow * k): one thread per POOLED element writes its k * k inputs (the winner gets the gradient, the others zero),
+// a quarter of the loads of the gather form.  The activation derivative needs only the winner's activation.
+// kChw: dy is CHW-flattened (it comes from a fully connected layer); one block per sample stages the row through
+// shared memory so the global reads stay coalesced.
+template <bool kChw>
+__global__ void maxpool_nhwc_bwd_scatter_kernel(const float* __restrict__ dy, const int32_t* __restrict__ argmax,
+                                                const float* __restrict__ a_prev, int act_prev, float* __restrict__ dx, int n,
+                                                int c, int h, int w, int oh, int ow, int k) {
+    extern __shared__ float sdy[];  // kChw: [c][oh * ow]
+    pdl_wait();
+    pdl_launch_dependents();
+    const int per = oh * ow * c, opix = oh * ow;
+    int s, i0, i1, step;
+    if (kChw) {
+        s = blockIdx.x;
+        for (int i = threadIdx.x; i < per; i += blockDim.x) sdy[i] = __ldg(dy + size_t(s) * per + i);
+        __syncthreads();
+        i0 = threadIdx.x, i1 = per, step = blockDim.x;
+    } else {
+        const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        if (gi >= (long long)n * per) return;
+        s = int(gi / per);
+        i0 = int(gi % per), i1 = i0 + 1, step = 1;
+    }
+    constexpr int kBatch = 4;  // items per thread whose dependent loads (argmax -> winner's activation) are in flight together
+    for (int ib = i0; ib < i1; ib += kBatch * step) {
+        int am[kBatch];
+        float g[kBatch];
+#pragma unroll
+        for (int u = 0; u < kBatch; u++) {
+            const int i = ib + u * step;
+            am[u] = i < i1 ? __ldg(argmax + size_t(s) * per + i) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < kBatch; u++) {
+            const int i = ib + u * step;
+            if (i >= i1) continue;
+            const int ch = i % c, ox = (i / c) % ow, oy = i / (c * ow);
+            g[u] = kChw ? sdy[ch * opix + oy * ow + ox] : __ldg(dy + size_t(s) * per + i);
+            if (a_prev) g[u] *= act_grad_from_output(act_prev, __ldg(a_prev + (size_t(s) * h * w + am[u]) * c + ch));
+        }
+#pragma unroll
+        for (int u = 0; u < kBatch; u++) {
+            const int i = ib + u * step;
+            if (i >= i1) continue;
+            const int ch = i % c, ox = (i / c) % ow, oy = i / (c * ow);
+            for (int dy_ = 0; dy_ < k; dy_++)
+                for (int dx_ = 0; dx_ < k; dx_++) {
+                    const int pix = (oy * k + dy_) * w + ox * k + dx_;
+                    dx[(size_t(s) * h * w + pix) * c + ch] = pix == am[u] ? g[u] : 0.0f;
+                }
+        }
+    }
+}
+
 }  // namespace
 
 int maxpool_nhwc_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride, int out_chw,
                      cudaStream_t st) {
     if (n <= 0 || c <= 0 || k <= 0 || stride <= 0 || h < k || w < k || !argmax) return set_error(kInvalidValue, "maxpool_nhwc_fwd: bad shape");
     const int oh = (h - k) / stride + 1, ow = (w - k) / stride + 1;
+    const size_t row = size_t(c) * oh * ow * sizeof(float);
+    if (out_chw && row <= 48 * 1024) {
+        B200CNN_CUDA(launch_kernel(maxpool_nhwc_fwd_chw_kernel, dim3(n), dim3(512), row, st, x, y, argmax, c, h, w, oh, ow, k, stride));
+        return 0;
+    }
     B200CNN_CUDA(launch_kernel(maxpool_nhwc_fwd_kernel, dim3(ceil_div(n * c * oh * ow, 256)), dim3(256), 0, st, x, y, argmax, n, c, h, w,
                                oh, ow, k, stride, out_chw));
     return 0;
@@ -137,6 +238,16 @@ int maxpool_nhwc_bwd(const float* dy, int dy_chw, const int32_t* argmax, const f
                      int h, int w, int k, int stride, cudaStream_t st) {
     if (n <= 0 || c <= 0 || k <= 0 || stride <= 0 || h < k || w < k || !argmax) return set_error(kInvalidValue, "maxpool_nhwc_bwd: bad shape");
     const int oh = (h - k) / stride + 1, ow = (w - k) / stride + 1;
+    const size_t row = size_t(c) * oh * ow * sizeof(float);
+    if (k == stride && h == oh * k && w == ow * k && (!dy_chw || row <= 48 * 1024)) {
+        if (dy_chw)
+            B200CNN_CUDA(launch_kernel(maxpool_nhwc_bwd_scatter_kernel<true>, dim3(n), dim3(512), row, st, dy, argmax, a_prev, act_prev, dx,
+                                       n, c, h, w, oh, ow, k));
+        else
+            B200CNN_CUDA(launch_kernel(maxpool_nhwc_bwd_scatter_kernel<false>, dim3(ceil_div(n * c * oh * ow, 256)), dim3(256), 0, st, dy,
+                                       argmax, a_prev, act_prev, dx, n, c, h, w, oh, ow, k));
+        return 0;
+    }
     B200CNN_CUDA(launch_kernel(maxpool_nhwc_bwd_kernel, dim3(ceil_div(n * c * h * w, 256)), dim3(256), 0, st, dy, dy_chw, argmax, a_prev,
                                act_prev, dx, n, c, h, w, oh, ow, k, stride));
     return 0;

@@ -104,6 +104,16 @@ int b200cnn_maxpool_nhwc_bwd(const float* dy, int dy_chw, const int32_t* argmax,
 size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s);
 int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const float* dz, int dz_is_chw, float* dw, float* db,
                                    int accumulate, void* scratch, const b200cnn_conv_shape* s, b200cnn_stream stream);
+/* First layer of the conv -> pool topology as one kernel: convolution (1 input channel, 3x3, stride 1, pad 1; x uint8
+ * scaled by 1/255, or float) + activation + 2x2 / stride-2 max pool.  yp / argmax: NHWC [n][oh/2][ow/2][oc] (argmax = index
+ * oy * ow + ox of the winning un-pooled pixel); a_full: NULL, or NHWC [n][oh][ow][oc] to also keep the un-pooled activations.
+ * The weight gradient is taken straight from the POOLED gradient dyp (only window winners contribute); yp is the pooled
+ * output (for act'), scratch as for b200cnn_conv2d_bwd_weight_nhwc. */
+int b200cnn_conv1_pool_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* a_full, float* yp, int32_t* argmax,
+                           const b200cnn_conv_shape* s, int act, b200cnn_stream stream);
+int b200cnn_conv1_pool_bwd_weight(const void* x, int x_is_u8, const float* dyp, const float* yp, const int32_t* argmax, int act,
+                                  float* dw, float* db, int accumulate, void* scratch, const b200cnn_conv_shape* s,
+                                  b200cnn_stream stream);
 
 /* ---- fully connected (K4, K6) ------------------------------------------------------------- */
 /* y[m][n] = act(sum_k x[m][k] w[n][k] + b[n]); ldy = row stride of y in floats (>= n).

@@ -200,6 +200,9 @@ class Engine:
         return {"ce_sum": ce, "mse_sum": mse, "correct": correct, "count": count}
 
     def layer_output(self, layer, batch):
+        """Activations of `layer` from the last forward pass as [batch, c*h*w] (CHW order whatever the device layout).
+        On the pooled topology's tensor-core path a training step does not store the un-pooled activations of the first
+        convolution (fused with its pool): layer 1 is available after forward() only."""
         n = self.layers[layer][1] * self.layers[layer][2] * self.layers[layer][3]
         out = np.empty((batch, n), dtype=np.float32)
         torch.cuda.synchronize()

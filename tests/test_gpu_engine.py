@@ -111,18 +111,24 @@ def test_graph_step_equals_eager_step_and_learns():
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("pool", [False, True])
 @pytest.mark.parametrize("backend,tol", [("simt", 2e-4), ("auto", 5e-3)])
-def test_gpu_engine_tracks_cpu_engine(backend, tol):
+def test_gpu_engine_tracks_cpu_engine(backend, tol, pool):
     """One mini-batch step on the GPU == the CPU engine (fp64) accumulating the same samples."""
-    from mpi_cuda_cnn_b200 import Engine
+    from mpi_cuda_cnn_b200 import Engine, mnist_layers, pool_layers
     from mpi_cuda_cnn_b200.ops import functional as F200
 
     F200.set_backend(backend)
     B = 16
-    eng = Engine(max_batch=B)
+    eng = Engine(pool_layers() if pool else mnist_layers(), max_batch=B)
     cpu = eng.init_params(seed=0)
     x, y = F200.synthetic_batch(B, seed=21)
     eng.train_step(x, y, 0.1 / B, use_graph=False)
+    if pool and backend == "auto":
+        # a training step on the fused conv + pool path keeps only the pooled activations of layer 1
+        with pytest.raises(RuntimeError, match="un-pooled"):
+            eng.layer_output(1, B)
+        assert eng.layer_output(2, B).shape == (B, 16 * 14 * 14)
     xs, ys = x.cpu().numpy().astype(np.float64) / 255.0, y.cpu().numpy()
     for i in range(B):
         cpu.set_inputs(xs[i])

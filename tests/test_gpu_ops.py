@@ -543,8 +543,10 @@ def test_tcgen05_conv3x3_stride1_backward_data(n, mask):
 
 @pytest.mark.parametrize("shape", [(5, 16, 28, 28), (3, 32, 14, 14)])
 @pytest.mark.parametrize("chw", [0, 1])
-def test_maxpool_nhwc_forward_backward(shape, chw):
-    """NHWC max pooling (2x2 / stride 2): NHWC or CHW-flattened output / incoming gradient, ReLU mask of the layer below."""
+@pytest.mark.parametrize("ks", [(2, 2), (3, 2)])
+def test_maxpool_nhwc_forward_backward(shape, chw, ks):
+    """NHWC max pooling: NHWC or CHW-flattened output / incoming gradient, ReLU mask of the layer below.  2x2 / stride 2
+    takes the per-sample and scatter kernels, 3x3 / stride 2 (overlapping windows) the general gather kernels."""
     import ctypes as C
 
     from mpi_cuda_cnn_b200 import _native as N
@@ -552,21 +554,76 @@ def test_maxpool_nhwc_forward_backward(shape, chw):
     lib = N.cuda()
     n, c, h, w = shape
     x = torch.relu(torch.randn(n, c, h, w, device="cuda")).requires_grad_(True)
-    ref = F.max_pool2d(x, 2, 2)
+    k, stride = ks
+    ref = F.max_pool2d(x, k, stride)
     dy = torch.randn_like(ref)
     ref.backward(dy)
     want_dx = x.grad * (x > 0)
     xn = x.detach().permute(0, 2, 3, 1).contiguous()
-    oh, ow = h // 2, w // 2
+    oh, ow = (h - k) // stride + 1, (w - k) // stride + 1
     y = torch.empty(n * c * oh * ow, device="cuda")
     arg = torch.empty(n * oh * ow * c, dtype=torch.int32, device="cuda")
     p = lambda t: C.c_void_p(t.data_ptr())
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    N.check(lib.b200cnn_maxpool_nhwc_fwd(p(xn), p(y), p(arg), n, c, h, w, 2, 2, chw, st), "maxpool_nhwc_fwd")
+    N.check(lib.b200cnn_maxpool_nhwc_fwd(p(xn), p(y), p(arg), n, c, h, w, k, stride, chw, st), "maxpool_nhwc_fwd")
     got = y.reshape(n, c, oh, ow) if chw else y.reshape(n, oh, ow, c).permute(0, 3, 1, 2)
     assert torch.equal(got, ref.detach())
     dyl = dy.contiguous() if chw else dy.permute(0, 2, 3, 1).contiguous()
     dx = torch.empty(n, h, w, c, device="cuda")
-    N.check(lib.b200cnn_maxpool_nhwc_bwd(p(dyl), chw, p(arg), p(xn), N.ACT_RELU, p(dx), n, c, h, w, 2, 2, st), "maxpool_nhwc_bwd")
+    N.check(lib.b200cnn_maxpool_nhwc_bwd(p(dyl), chw, p(arg), p(xn), N.ACT_RELU, p(dx), n, c, h, w, k, stride, st), "maxpool_nhwc_bwd")
     torch.cuda.synchronize()
     assert float((dx.permute(0, 3, 1, 2) - want_dx).abs().max()) < 1e-6
+
+
+@pytest.mark.parametrize("n", [1, 7, 256, 300])
+@pytest.mark.parametrize("u8", [1, 0])
+def test_conv1_pool_fused_forward_and_weight_gradient(n, u8):
+    """First layer of the pooled topology as one kernel (conv 1 -> 16, 3x3 / s1 / p1 + ReLU + 2x2 max pool) and its weight
+    gradient taken from the POOLED gradient, against PyTorch fp32 autograd through conv -> relu -> max_pool."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    torch.backends.cudnn.allow_tf32 = False
+    xi = torch.randint(0, 256, (n, 1, 28, 28), device="cuda", dtype=torch.uint8)
+    xf = xi.float() / 255.0
+    x_dev = xi if u8 else xf.contiguous()
+    w = (0.3 * torch.randn(16, 1, 3, 3, device="cuda")).requires_grad_(True)
+    b = (0.1 * torch.randn(16, device="cuda")).requires_grad_(True)
+    a = torch.relu(F.conv2d(xf, w, b, 1, 1))
+    yp_ref = F.max_pool2d(a, 2, 2)
+    dyp = torch.randn_like(yp_ref)
+    yp_ref.backward(dyp)
+    shp = N.ConvShape(n, 1, 28, 28, 16, 28, 28, 3, 1, 1)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for keep in (1, 0):
+        a_full = torch.full((n, 28, 28, 16), 9.0, device="cuda")
+        yp = torch.full((n, 14, 14, 16), 9.0, device="cuda")
+        arg = torch.full((n, 14, 14, 16), -5, dtype=torch.int32, device="cuda")
+        N.check(lib.b200cnn_conv1_pool_fwd(p(x_dev), u8, p(w.detach()), p(b.detach()), p(a_full) if keep else None, p(yp), p(arg),
+                                           C.byref(shp), N.ACT_RELU, st), "conv1_pool_fwd")
+        torch.cuda.synchronize()
+        _close(yp.permute(0, 3, 1, 2), yp_ref.detach(), 1e-5)
+        if keep:
+            _close(a_full.permute(0, 3, 1, 2), a.detach(), 1e-5)
+            # the recorded winner holds the pooled value and lies inside its own window
+            win = torch.gather(a_full.reshape(n, 784, 16), 1, arg.reshape(n, 196, 16).long())
+            assert torch.equal(win, yp.reshape(n, 196, 16))
+            q = torch.arange(196, device="cuda").reshape(1, 196, 1)
+            ay, ax = arg.reshape(n, 196, 16) // 28, arg.reshape(n, 196, 16) % 28
+            assert bool(((ay // 2) == (q // 14)).all()) and bool(((ax // 2) == (q % 14)).all())
+        else:
+            assert bool((a_full == 9.0).all())
+    scratch = torch.zeros(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp)), dtype=torch.uint8, device="cuda")
+    buf = torch.full((16 * 9 + 16 + 64,), 7.0, device="cuda")
+    dw, db = buf[16:16 + 144], buf[16 + 144 + 16:16 + 144 + 32]
+    dyn = dyp.permute(0, 2, 3, 1).contiguous()
+    for rep in range(2):  # the completion counter in the scratch header must reset itself
+        N.check(lib.b200cnn_conv1_pool_bwd_weight(p(x_dev), u8, p(dyn), p(yp), p(arg), N.ACT_RELU, p(dw), p(db), 0, p(scratch),
+                                                  C.byref(shp), st), "conv1_pool_bwd_weight")
+        torch.cuda.synchronize()
+        _close(dw.reshape(16, 1, 3, 3), w.grad, 1e-4)
+        _close(db, b.grad, 1e-4)
+    assert bool((buf[:16] == 7.0).all()) and bool((buf[16 + 144:16 + 144 + 16] == 7.0).all()) and bool((buf[16 + 144 + 32:] == 7.0).all())
