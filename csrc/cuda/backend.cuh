@@ -55,19 +55,29 @@ int tc_fc_mid(const float* h1, const float* w2, const float* b2, const float* w3
 
 // tc_conv.cu: implicit-GEMM 3x3 convolutions on NHWC activations
 bool tc_conv3x3_fwd_supported(const b200cnn_conv_shape* s);
+// early_w (here and below): the caller guarantees that the kernel launched just before this one on the stream does not
+// write the weights (inside the engine it is always another layer's kernel), so their gather into shared memory may run
+// BEFORE griddepcontrol.wait and overlap that kernel's tail.
 int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s,
-                   int act, cudaStream_t st, int nhwc_out = 0);
+                   int act, cudaStream_t st, int nhwc_out = 0, int early_w = 0);
 // stride-1 counterpart of tc_conv3x3s2_bwd_data (32 -> 16 channels, same spatial size): dz / a_prev / dx all NHWC
 bool tc_conv3x3s1_bwd_data_supported(const b200cnn_conv_shape* s);
 int tc_conv3x3s1_bwd_data(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
-                          const b200cnn_conv_shape* s, cudaStream_t st);
+                          const b200cnn_conv_shape* s, cudaStream_t st, int early_w = 0);
+// tc_conv_halo.cu: the stride-1 convolutions with ONE halo load per tile, taps by descriptor shifts (used by the two above)
+bool tc_conv3x3s1_halo_fwd_supported(const b200cnn_conv_shape* s);
+bool tc_conv3x3s1_halo_bwd_data_supported(const b200cnn_conv_shape* s);
+int tc_conv3x3s1_halo_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s, int act,
+                          cudaStream_t st, int nhwc_out, int early_w = 0);
+int tc_conv3x3s1_halo_bwd_data(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
+                               const b200cnn_conv_shape* s, cudaStream_t st, int early_w = 0);
 // pool.cu: NHWC max pooling for the tensor-core chain of the pooled topology
 int maxpool_nhwc_fwd(const float* x, float* y, int32_t* argmax, int n, int c, int h, int w, int k, int stride, int out_chw, cudaStream_t st);
 int maxpool_nhwc_bwd(const float* dy, int dy_chw, const int32_t* argmax, const float* a_prev, int act_prev, float* dx, int n, int c,
                      int h, int w, int k, int stride, cudaStream_t st);
 bool tc_conv3x3s2_bwd_data_supported(const b200cnn_conv_shape* s);
 int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
-                          float* dx_nhwc, const b200cnn_conv_shape* s, cudaStream_t st);
+                          float* dx_nhwc, const b200cnn_conv_shape* s, cudaStream_t st, int early_w = 0);
 
 // tc_conv_wgrad.cu: split-K implicit-GEMM weight gradient of the 16->32 channel 3x3/s2 convolution (14x14 -> 7x7)
 bool tc_conv3x3s2_bwd_weight_supported(const b200cnn_conv_shape* s);

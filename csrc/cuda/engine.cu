@@ -163,6 +163,12 @@ bool use_mid(const b200cnn_engine* e, int batch) {
     return tc_fc_mid_supported(batch, L[n - 3].nnodes, L[n - 2].nnodes, L[n - 1].nnodes, L[n - 1].ld);
 }
 
+// The tensor-core convolutions gather their weights into shared memory before griddepcontrol.wait: inside a step the kernel
+// in front of them on the stream is always another layer's kernel (never an update), and that kernel released its
+// dependents only after its own wait, i.e. after everything older — including the previous step's update — was complete.
+// (A data-parallel update arriving from the peers is ordered by an event, a full dependency: the kernel does not start early.)
+constexpr int kEarlyW = 1;
+
 // Forward through layers [1, stop).
 int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint8_t* labels, int batch,
                     cudaStream_t st, int* launches, size_t stop = ~size_t(0)) {
@@ -192,10 +198,11 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
                 else if ((fast || poolc) && li == 1)  // first conv: CUDA cores (1 input channel), NHWC output for the TMA loads below
                     rc = simt_conv2d_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, l.a, &s, l.act, 1, st);
                 else if (poolc && li == 3)  // 196 pixels per image: two bands of the implicit GEMM, NHWC output for the pool
-                    rc = tc_conv3x3_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a, 0, &s, l.act, st, 1);
+                    rc = tc_conv3x3_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a, 0, &s, l.act, st, 1,
+                                        kEarlyW);
                 else if (fast && li == 2)  // implicit GEMM on tcgen05, output CHW-flattened for the FC layer
                     rc = tc_conv3x3_fwd(static_cast<const float*>(in), e->params + l.w_off, e->params + l.b_off, l.a, l.ld, &s,
-                                        l.act, st);
+                                        l.act, st, 0, kEarlyW);
                 else
                     rc = b200cnn_conv2d_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, l.a, &s, l.act, st);
                 break;
@@ -376,9 +383,9 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             } else {
                 const b200cnn_conv_shape s = conv_shape(p, l, batch);
                 if (fast && li == 2)
-                    rc = tc_conv3x3s2_bwd_data(l.dz, /*dz_is_chw=*/1, e->params + l.w_off, p.a, p.act, p.dz, &s, st);
+                    rc = tc_conv3x3s2_bwd_data(l.dz, /*dz_is_chw=*/1, e->params + l.w_off, p.a, p.act, p.dz, &s, st, kEarlyW);
                 else if (poolc && li == 3)  // the layer below is a pool: no activation derivative to apply
-                    rc = tc_conv3x3s1_bwd_data(l.dz, e->params + l.w_off, nullptr, B200CNN_ACT_NONE, p.dz, &s, st);
+                    rc = tc_conv3x3s1_bwd_data(l.dz, e->params + l.w_off, nullptr, B200CNN_ACT_NONE, p.dz, &s, st, kEarlyW);
                 else
                     rc = b200cnn_conv2d_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, &s, st);
             }
@@ -850,6 +857,7 @@ static int train_step_impl(b200cnn_engine* e, const void* images, int x_is_u8, c
             return rc;
         }
         if (ce != cudaSuccess) return set_error(int(ce), "engine_train_step: capture failed: %s", cudaGetErrorString(ce));
+        if (const char* dot = getenv("B200CNN_GRAPH_DOT")) cudaGraphDebugDotPrint(graph, dot, cudaGraphDebugDotFlagsVerbose);  // diagnosis
         const cudaError_t ie = cudaGraphInstantiate(&ge->exec[par], graph, 0);
         cudaGraphDestroy(graph);
         if (ie != cudaSuccess) return set_error(int(ie), "engine_train_step: instantiate failed: %s", cudaGetErrorString(ie));

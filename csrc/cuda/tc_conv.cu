@@ -45,6 +45,7 @@ struct ConvFwdArgs {
     int tiles;      // > 1: an image has more than 128 output pixels and is cut into `tiles` bands of oh_t output rows,
     int oh_t;       //      one band (and one sample) per CTA; tiles == 1: oh_t = oh and `group` samples per CTA
     int nhwc_out;   // output [n][oh][ow][oc] (feeds another NHWC layer) instead of CHW-flattened rows
+    int early_w;    // the weights are not written by the kernel in front of this one: gather them BEFORE griddepcontrol.wait
 };
 
 // ---- forward -------------------------------------------------------------------------------------
@@ -81,6 +82,27 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Weights: OIHW -> per-tap K-major [oc][c] tiles in the 64-byte-swizzle layout
+    // (16-byte chunk index ^= (row >> 1) & 3, cute Swizzle<2,4,3>).  Every load of a thread is in flight at once: the
+    // gather is a chain of L2 round trips otherwise.
+    auto gather_weights = [&]() {
+        constexpr int kW = OC * kCin * kTaps, kStride = kConvThreads - 64, kBatch = 12;
+        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += kBatch * kStride) {  // i walks OIHW linearly
+            float v[kBatch];
+#pragma unroll
+            for (int u = 0; u < kBatch; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
+#pragma unroll
+            for (int u = 0; u < kBatch; u++) {
+                const int i = i0 + u * kStride;
+                if (i >= kW) break;
+                const int t = i % kTaps, c = (i / kTaps) % kCin, oc = i / (kTaps * kCin);
+                const int chunk = (c >> 2) ^ ((oc >> 1) & 3);
+                *reinterpret_cast<float*>(b_tiles + t * kBTile + oc * 64 + chunk * 16 + (c & 3) * 4) = v[u];
+            }
+        }
+        fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor-core (async) proxy
+    };
+    if (a.early_w && warp >= 2) gather_weights();  // overlaps the tail of the kernel in front
     pdl_wait();
     pdl_launch_dependents();
 
@@ -92,24 +114,8 @@ tc_conv3x3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
             for (int t = 0; t < kTaps; t++)
                 tma_load_4d(a_tiles + t * kATile, &tmap_x, full_bar, 0, t % 3 - a.pad, band * a.oh_t * a.stride + t / 3 - a.pad, n0);
         }
-    } else if (warp >= 2) {
-        // Weights: OIHW -> per-tap K-major [oc][c] tiles in the 64-byte-swizzle layout
-        // (16-byte chunk index ^= (row >> 1) & 3, cute Swizzle<2,4,3>).
-        constexpr int kW = OC * kCin * kTaps, kStride = kConvThreads - 64;
-        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += 4 * kStride) {  // i walks OIHW linearly; 4 loads in flight
-            float v[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const int i = i0 + u * kStride;
-                if (i >= kW) break;
-                const int t = i % kTaps, c = (i / kTaps) % kCin, oc = i / (kTaps * kCin);
-                const int chunk = (c >> 2) ^ ((oc >> 1) & 3);
-                *reinterpret_cast<float*>(b_tiles + t * kBTile + oc * 64 + chunk * 16 + (c & 3) * 4) = v[u];
-            }
-        }
-        fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor-core (async) proxy
+    } else if (warp >= 2 && !a.early_w) {
+        gather_weights();
     }
     __syncthreads();
 
@@ -222,6 +228,7 @@ struct ConvBwdArgs {
     float* dx;            // NHWC [n][h][w][c]
     int n, oh, ow, h, w_in, group;
     int act_prev;
+    int early_w;  // as in ConvFwdArgs
 };
 
 // Output-gradient channels OC = 32 (one 128-byte swizzle row per pixel), input channels C = 16.
@@ -257,6 +264,25 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Weights per tap as the B operand [n = c][k = oc], K-major 128-byte rows, 128B swizzle (16-byte chunk ^= row & 7);
+    // every load of a thread in flight at once.
+    auto gather_weights = [&]() {
+        constexpr int kW = OC * C * kTaps, kStride = kConvThreads - 64, kBatch = 12;
+        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += kBatch * kStride) {
+            float v[kBatch];
+#pragma unroll
+            for (int u = 0; u < kBatch; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
+#pragma unroll
+            for (int u = 0; u < kBatch; u++) {
+                const int i = i0 + u * kStride;
+                if (i >= kW) break;
+                const int t = i % kTaps, c = (i / kTaps) % C, oc = i / (kTaps * C);
+                const int chunk = (oc >> 2) ^ (c & 7);
+                *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = v[u];
+            }
+        }
+    };
+    if (a.early_w && warp >= 2) gather_weights();  // overlaps the tail of the kernel in front
     pdl_wait();
     pdl_launch_dependents();
 
@@ -311,24 +337,7 @@ tc_conv3x3s2_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvBw
                 tma_load_4d(a_tiles + sft * kATile, &tmap_dz, full_bar, 0, sft & 1, sft >> 1, n0);
         }
     }
-    if (warp >= 2) {
-        // Weights per tap as the B operand [n = c][k = oc], K-major 128-byte rows, 128B swizzle
-        // (16-byte chunk ^= row & 7).
-        constexpr int kW = OC * C * kTaps, kStride = kConvThreads - 64;
-        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += 4 * kStride) {
-            float v[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const int i = i0 + u * kStride;
-                if (i >= kW) break;
-                const int t = i % kTaps, c = (i / kTaps) % C, oc = i / (kTaps * C);
-                const int chunk = (oc >> 2) ^ (c & 7);
-                *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = v[u];
-            }
-        }
-    }
+    if (warp >= 2 && !a.early_w) gather_weights();
     fence_proxy_async_smem();
     __syncthreads();
 
@@ -428,6 +437,7 @@ struct ConvS1BwdArgs {
     float* dx;            // NHWC [n][h][w][c]
     int n, h, w_in, tiles, h_t;
     int act_prev;
+    int early_w;  // as in ConvFwdArgs
 };
 
 template <int OC, int C>
@@ -460,6 +470,28 @@ tc_conv3x3s1_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvS1
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Weights per tap as the B operand [n = c][k = oc], K-major 128-byte rows, 128B swizzle (16-byte chunk ^= row & 7);
+    // every load of a thread in flight at once.
+    auto gather_weights = [&]() {
+        constexpr int kW = OC * C * kTaps, kStride = kConvThreads - 64, kBatch = 12;
+        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += kBatch * kStride) {
+            float v[kBatch];
+#pragma unroll
+            for (int u = 0; u < kBatch; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
+#pragma unroll
+            for (int u = 0; u < kBatch; u++) {
+                const int i = i0 + u * kStride;
+                if (i >= kW) break;
+                const int t = i % kTaps, c = (i / kTaps) % C, oc = i / (kTaps * C);
+                const int chunk = (oc >> 2) ^ (c & 7);
+                *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = v[u];
+            }
+        }
+    };
+    if (a.early_w && warp >= 2) {  // overlaps the tail of the kernel in front
+        gather_weights();
+        fence_proxy_async_smem();
+    }
     pdl_wait();
     pdl_launch_dependents();
 
@@ -470,22 +502,8 @@ tc_conv3x3s1_bwd_data_kernel(const __grid_constant__ CUtensorMap tmap_dz, ConvS1
             for (int t = 0; t < kTaps; t++)  // tap (ky, kx) reads dz at (y + 1 - ky, x + 1 - kx)
                 tma_load_4d(a_tiles + t * kATile, &tmap_dz, full_bar, 0, 1 - t % 3, band * a.h_t + 1 - t / 3, n0);
         }
-    } else if (warp >= 2) {
-        // Weights per tap as the B operand [n = c][k = oc], K-major 128-byte rows, 128B swizzle (chunk ^= row & 7).
-        constexpr int kW = OC * C * kTaps, kStride = kConvThreads - 64;
-        for (int i0 = threadIdx.x - 64; i0 < kW; i0 += 4 * kStride) {
-            float v[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) v[u] = (i0 + u * kStride < kW) ? __ldg(a.w + i0 + u * kStride) : 0.f;
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const int i = i0 + u * kStride;
-                if (i >= kW) break;
-                const int t = i % kTaps, c = (i / kTaps) % C, oc = i / (kTaps * C);
-                const int chunk = (oc >> 2) ^ (c & 7);
-                *reinterpret_cast<float*>(b_tiles + t * kBTile + c * 128 + chunk * 16 + (oc & 3) * 4) = v[u];
-            }
-        }
+    } else if (warp >= 2 && !a.early_w) {
+        gather_weights();
         fence_proxy_async_smem();
     }
     __syncthreads();
@@ -559,8 +577,10 @@ bool tc_conv3x3_fwd_supported(const b200cnn_conv_shape* s) {
 
 // x: NHWC [n][h][w][16]; y: [n][ldy] with the sample's outputs CHW-flattened (ldy >= oc*oh*ow).
 int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y, int ldy, const b200cnn_conv_shape* s,
-                   int act, cudaStream_t st, int nhwc_out) {
+                   int act, cudaStream_t st, int nhwc_out, int early_w) {
     if (!tc_conv3x3_fwd_supported(s)) return set_error(kInvalidValue, "tc_conv3x3_fwd: unsupported shape");
+    if (tc_conv3x3s1_halo_fwd_supported(s))  // stride 1: one operand load with a halo instead of nine boxes (tc_conv_halo.cu)
+        return tc_conv3x3s1_halo_fwd(x_nhwc, w, b, y, ldy, s, act, st, nhwc_out, early_w);
     const int pix = s->oh * s->ow;
     const int tiles = fwd_tiles(s), oh_t = s->oh / tiles;
     const int group = tiles > 1 ? 1 : kTileRows / pix;
@@ -595,7 +615,7 @@ int tc_conv3x3_fwd(const float* x_nhwc, const float* w, const float* b, float* y
         const uint32_t ybox[2] = {uint32_t(bw), uint32_t(group)};
         if (int rc = encode_tmap_f32(&tmy, y, 2, ydims, ystr, ybox, nullptr, 0)) return rc;
     }
-    ConvFwdArgs a{w, b, y, ldy, s->n, s->oc, s->oh, s->ow, s->pad, group, act, s->stride, bw, tiles, oh_t, nhwc_out};
+    ConvFwdArgs a{w, b, y, ldy, s->n, s->oc, s->oh, s->ow, s->pad, group, act, s->stride, bw, tiles, oh_t, nhwc_out, early_w};
     const int grid = tiles > 1 ? s->n * tiles : ceil_div(s->n, group);
 #define B200CNN_LAUNCH_FWD(OCV)                                                                                   \
     do {                                                                                                          \
@@ -623,7 +643,7 @@ bool tc_conv3x3s2_bwd_data_supported(const b200cnn_conv_shape* s) {
 
 // dz: NHWC [n][oh][ow][32], or CHW [n][32][oh][ow] when dz_is_chw; a_prev / dx: NHWC [n][h][w][16].
 int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const float* a_prev_nhwc, int act_prev,
-                          float* dx_nhwc, const b200cnn_conv_shape* s, cudaStream_t st) {
+                          float* dx_nhwc, const b200cnn_conv_shape* s, cudaStream_t st, int early_w) {
     const float* dz_nhwc = dz;
     if (!tc_conv3x3s2_bwd_data_supported(s)) return set_error(kInvalidValue, "tc_conv3x3s2_bwd_data: unsupported shape");
     const int pix = s->oh * s->ow;
@@ -633,7 +653,7 @@ int tc_conv3x3s2_bwd_data(const float* dz, int dz_is_chw, const float* w, const 
     const uint64_t strides[4] = {0, uint64_t(s->oc) * 4, uint64_t(s->ow) * s->oc * 4, uint64_t(pix) * s->oc * 4};
     const uint32_t box[4] = {uint32_t(s->oc), uint32_t(s->ow), uint32_t(s->oh), uint32_t(group)};
     if (int rc = encode_tmap_f32(&tm, dz_nhwc, 4, dims, strides, box, nullptr, 128)) return rc;
-    ConvBwdArgs a{dz_is_chw ? dz : nullptr, w, a_prev_nhwc, dx_nhwc, s->n, s->oh, s->ow, s->h, s->w, group, act_prev};
+    ConvBwdArgs a{dz_is_chw ? dz : nullptr, w, a_prev_nhwc, dx_nhwc, s->n, s->oh, s->ow, s->h, s->w, group, act_prev, early_w};
     auto kern = tc_conv3x3s2_bwd_data_kernel<32, 16>;
     constexpr size_t smem = 4 * size_t(kTileRows) * 32 * 4 + kTaps * 16 * 32 * 4 + size_t(kTileRows) * 32 * 4 + 1024 + 64;
     static bool configured = false;
@@ -659,15 +679,16 @@ bool tc_conv3x3s1_bwd_data_supported(const b200cnn_conv_shape* s) {
 
 // dz: NHWC [n][h][w][32]; a_prev / dx: NHWC [n][h][w][16].
 int tc_conv3x3s1_bwd_data(const float* dz_nhwc, const float* w, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
-                          const b200cnn_conv_shape* s, cudaStream_t st) {
+                          const b200cnn_conv_shape* s, cudaStream_t st, int early_w) {
     if (!tc_conv3x3s1_bwd_data_supported(s)) return set_error(kInvalidValue, "tc_conv3x3s1_bwd_data: unsupported shape");
+    if (tc_conv3x3s1_halo_bwd_data_supported(s)) return tc_conv3x3s1_halo_bwd_data(dz_nhwc, w, a_prev_nhwc, act_prev, dx_nhwc, s, st, early_w);
     const int tiles = s1_tiles(s), h_t = s->h / tiles;
     CUtensorMap tm;
     const uint64_t dims[4] = {uint64_t(s->oc), uint64_t(s->ow), uint64_t(s->oh), uint64_t(s->n)};
     const uint64_t strides[4] = {0, uint64_t(s->oc) * 4, uint64_t(s->ow) * s->oc * 4, uint64_t(s->oh) * s->ow * s->oc * 4};
     const uint32_t box[4] = {uint32_t(s->oc), uint32_t(s->ow), uint32_t(h_t), 1};
     if (int rc = encode_tmap_f32(&tm, dz_nhwc, 4, dims, strides, box, nullptr, 128)) return rc;
-    ConvS1BwdArgs a{w, a_prev_nhwc, dx_nhwc, s->n, s->h, s->w, tiles, h_t, act_prev};
+    ConvS1BwdArgs a{w, a_prev_nhwc, dx_nhwc, s->n, s->h, s->w, tiles, h_t, act_prev, early_w};
     auto kern = tc_conv3x3s1_bwd_data_kernel<32, 16>;
     constexpr size_t smem = size_t(kTaps) * (kTileRows * 32 * 4 + 16 * 32 * 4) + 1024 + 64;
     static bool configured = false;

@@ -2,7 +2,7 @@
 
 Runs the graph-captured step under torch.profiler (Kineto/CUPTI records the kernels our .so launches too), takes
 the kernels of one step in the middle of the run and prints start offset, duration, stream and the gap to the
-previous kernel on the same stream.  Usage: python tools/timeline.py [batch] [steps] [--pool] [--simt]
+previous kernel on the same stream.  Usage: python tools/timeline.py [batch] [steps] [--pool] [--simt] [--eager]
 """
 import os
 import sys
@@ -14,7 +14,7 @@ from torch.profiler import ProfilerActivity, profile
 from mpi_cuda_cnn_b200.engine import Engine
 from mpi_cuda_cnn_b200.ops import functional as F200
 
-POOL, SIMT = "--pool" in sys.argv, "--simt" in sys.argv
+POOL, SIMT, EAGER = "--pool" in sys.argv, "--simt" in sys.argv, "--eager" in sys.argv
 _pos = [a for a in sys.argv[1:] if not a.startswith("--")]
 B = int(_pos[0]) if len(_pos) > 0 else 256
 STEPS = int(_pos[1]) if len(_pos) > 1 else 40
@@ -46,11 +46,11 @@ ys = [y[i * B:(i + 1) * B].contiguous() for i in range(8)]
 stream = torch.cuda.Stream(device=dev)
 with torch.cuda.stream(stream):
     for i in range(20):
-        eng.train_step(xs[i % 8], ys[i % 8], 0.1 / B, stream=stream)
+        eng.train_step(xs[i % 8], ys[i % 8], 0.1 / B, stream=stream, use_graph=not EAGER)
     torch.cuda.synchronize()
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
         for i in range(STEPS):
-            eng.train_step(xs[i % 8], ys[i % 8], 0.1 / B, stream=stream)
+            eng.train_step(xs[i % 8], ys[i % 8], 0.1 / B, stream=stream, use_graph=not EAGER)
         torch.cuda.synchronize()
 ev = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA and "emcpy" not in e.name and "emset" not in e.name]
 ev.sort(key=lambda e: e.time_range.start)
