@@ -85,6 +85,12 @@ size_t tc_conv3x3s2_bwd_weight_scratch_floats(int n);
 int tc_conv3x3s2_bwd_weight(const float* x_nhwc, const float* dz, int dz_is_chw, float* dw, float* db, int accumulate,
                             float* part, const b200cnn_conv_shape* s, cudaStream_t st);
 
+// ... and of the stride-1 16->32 channel convolution at 14x14 (pooled topology): x, dz NHWC
+bool tc_conv3x3s1_bwd_weight_supported(const b200cnn_conv_shape* s);
+size_t tc_conv3x3s1_bwd_weight_scratch_floats(int n);
+int tc_conv3x3s1_bwd_weight(const float* x_nhwc, const float* dz_nhwc, float* dw, float* db, int accumulate, float* part,
+                            const b200cnn_conv_shape* s, cudaStream_t st);
+
 // tc_conv1_wgrad.cu: weight gradient of the 1 -> 16 channel first convolution on the tensor cores (opt-in, see the file)
 bool tc_conv1_bwd_weight_enabled();
 bool tc_conv1_bwd_weight_supported(const b200cnn_conv_shape* s, int max_partials);
@@ -98,6 +104,7 @@ bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
 int nhwc_bwd_weight_chunks(int n, int* spb_out);
 int nhwc_bwd_weight_chunks_for(const b200cnn_conv_shape* s, int* spb_out);
 size_t nhwc_bwd_weight_smem_bytes(const b200cnn_conv_shape* s);
+size_t nhwc_bwd_weight_scratch_floats(const b200cnn_conv_shape* s);
 int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw, float* dw, float* db, int accumulate,
                          float* partials, unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st,
                          float* sgd_w = nullptr, float* sgd_b = nullptr, const float* lr_dev = nullptr,

@@ -42,6 +42,19 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 
 bool pdl_enabled();  // B200CNN_PDL=0 in the environment turns the launch attribute off
 
+// Kernels launched on the "critical" stream of the calling thread get the highest launch priority the device offers:
+// the training step forks its weight-gradient kernels onto a side stream, and when one of those still has CTAs waiting
+// for an SM (grids of 2+ waves) the block scheduler would otherwise finish dispatching it before it starts the kernel
+// that continues the critical path.  (Captured into CUDA-graph kernel nodes like any other launch attribute.)
+// B200CNN_PRIORITY=0 turns it off.
+struct CriticalStreamScope {
+    explicit CriticalStreamScope(cudaStream_t st);
+    ~CriticalStreamScope();
+    cudaStream_t saved;
+};
+cudaStream_t critical_stream();  // of this thread; nullptr = none
+int critical_priority();         // 0 = none / disabled
+
 // cluster_z > 1: thread-block clusters of (1, 1, cluster_z) CTAs (grid.z must be a multiple of it).
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_kernel_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
@@ -51,8 +64,13 @@ inline cudaError_t launch_kernel_cluster(void (*kernel)(KArgs...), dim3 grid, di
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[2];
+    cudaLaunchAttribute attr[3];
     int n = 0;
+    if (st != nullptr && st == critical_stream() && critical_priority() != 0) {
+        attr[n].id = cudaLaunchAttributePriority;
+        attr[n].val.priority = critical_priority();
+        n++;
+    }
     if (pdl_enabled()) {
         attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         attr[n].val.programmaticStreamSerializationAllowed = 1;

@@ -472,6 +472,15 @@ int nhwc_bwd_weight_chunks_for(const b200cnn_conv_shape* s, int* spb_out) {
     return ceil_div(s->n, spb);
 }
 
+// Floats of partial sums behind the 128-byte header that nhwc_conv_bwd_weight may use for this layer (whichever kernel
+// it picks): what b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes and the engine allocate.
+size_t nhwc_bwd_weight_scratch_floats(const b200cnn_conv_shape* s) {
+    size_t need = size_t(nhwc_bwd_weight_chunks_for(s, nullptr)) * (size_t(s->oc) * s->c * s->k * s->k + s->oc);
+    if (tc_conv3x3s2_bwd_weight_supported(s)) need = std::max(need, tc_conv3x3s2_bwd_weight_scratch_floats(s->n));
+    if (tc_conv3x3s1_bwd_weight_supported(s)) need = std::max(need, tc_conv3x3s1_bwd_weight_scratch_floats(s->n));
+    return need;
+}
+
 // Fused first layer of the pooled topology (see the kernels): conv 3x3 / stride 1 / pad 1 on one input channel, then a
 // 2x2 / stride-2 max pool.
 bool conv1_pool_supported(const b200cnn_conv_shape* s, int pool_k, int pool_stride) {
@@ -568,10 +577,12 @@ int nhwc_conv_bwd_weight(const void* x, int x_is_u8, const float* dz, int dz_chw
             if (smem > 48 * 1024) cudaFuncSetAttribute(conv_bwd_weight_c1_nhwc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
             B200CNN_CUDA(launch_kernel(conv_bwd_weight_c1_nhwc_kernel<float>, dim3(chunks), dim3(kC1Threads), smem, st, static_cast<const float*>(x), dz, partials, *s, spb, 1.0f, dw, db, accumulate, counter, sgd_w, sgd_b, lr_dev));
         }
-    } else if (tc_wgrad_enabled() && !x_is_u8 && tc_conv3x3s2_bwd_weight_supported(s) &&
-               tc_conv3x3s2_bwd_weight_scratch_floats(s->n) <= size_t(chunks) * (nw + s->oc)) {
+    } else if (tc_wgrad_enabled() && !x_is_u8 && tc_conv3x3s2_bwd_weight_supported(s)) {
         // tensor cores: split-K implicit GEMM + a small reduce kernel over the n/8 partial tiles
         return tc_conv3x3s2_bwd_weight(static_cast<const float*>(x), dz, dz_chw, dw, db, accumulate, partials, s, st);
+    } else if (tc_wgrad_enabled() && !x_is_u8 && !dz_chw && tc_conv3x3s1_bwd_weight_supported(s)) {
+        // the same split-K implicit GEMM over the stride-1 views (pooled topology)
+        return tc_conv3x3s1_bwd_weight(static_cast<const float*>(x), dz, dw, db, accumulate, partials, s, st);
     } else {
         const int work = (s->oc / 4) * (s->c / 4) * kk;
         const int threads = ((work + 31) / 32) * 32;

@@ -545,10 +545,13 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
                         nhwc_bwd_weight_supported(&s1, 1) && nhwc_bwd_weight_supported(&s2, 0) && s1.oc % 16 == 0 &&
                         tc_linear_bwd_data_supported(max_batch, e->layers[3].nnodes, e->layers[2].nnodes, e->layers[3].ld);
         if (e->fast_chain) {
-            size_t chunks = 0;  // worst case over every legal batch (same non-monotonic shape as above, period 148)
-            for (int n = 1; n <= max_batch; n++) chunks = std::max(chunks, size_t(nhwc_bwd_weight_chunks(n, nullptr)));
-            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[2].nw + e->layers[2].nb) * sizeof(float) + 128);
-            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float) + 128);
+            // worst case over every legal batch (same non-monotonic shape as above, period 148)
+            b200cnn_conv_shape t1 = s1, t2 = s2;
+            for (int n = 1; n <= max_batch; n++) {
+                t1.n = t2.n = n;
+                scratch_bytes = std::max(scratch_bytes, nhwc_bwd_weight_scratch_floats(&t1) * sizeof(float) + 128);
+                scratch_bytes = std::max(scratch_bytes, nhwc_bwd_weight_scratch_floats(&t2) * sizeof(float) + 128);
+            }
         }
     }
     // The pooled variant conv -> pool -> conv -> pool -> FC: first convolution on the CUDA cores (one input channel),
@@ -563,15 +566,12 @@ extern "C" b200cnn_engine* b200cnn_engine_create(const b200cnn_layer_desc* layer
                         nhwc_bwd_weight_supported(&s1, 1) && nhwc_bwd_weight_supported(&s3, 0) &&
                         nhwc_bwd_weight_smem_bytes(&s1) <= kSmemLimit && nhwc_bwd_weight_smem_bytes(&s3) <= kSmemLimit;
         if (e->pool_chain) {
-            size_t chunks = 0, chunks3 = 0;
-            b200cnn_conv_shape t3 = s3;
+            b200cnn_conv_shape t1 = s1, t3 = s3;
             for (int n = 1; n <= max_batch; n++) {
-                t3.n = n;
-                chunks = std::max(chunks, size_t(nhwc_bwd_weight_chunks(n, nullptr)));
-                chunks3 = std::max(chunks3, size_t(nhwc_bwd_weight_chunks_for(&t3, nullptr)));
+                t1.n = t3.n = n;
+                scratch_bytes = std::max(scratch_bytes, nhwc_bwd_weight_scratch_floats(&t1) * sizeof(float) + 128);
+                scratch_bytes = std::max(scratch_bytes, nhwc_bwd_weight_scratch_floats(&t3) * sizeof(float) + 128);
             }
-            scratch_bytes = std::max(scratch_bytes, chunks3 * size_t(e->layers[3].nw + e->layers[3].nb) * sizeof(float) + 128);
-            scratch_bytes = std::max(scratch_bytes, chunks * size_t(e->layers[1].nw + e->layers[1].nb) * sizeof(float) + 128);
             static const bool fuse_env = [] {
                 const char* v = getenv("B200CNN_POOL_FUSED");  // B200CNN_POOL_FUSED=0: separate conv / pool kernels (A/B timing)
                 return !(v && v[0] == '0');
@@ -748,6 +748,7 @@ static int enqueue_step(b200cnn_engine* e, const void* images, int is_u8, const 
     const bool chain = use_chain(e, batch);
     const bool mid = !chain && use_mid(e, batch);
     const bool head = !chain && (mid || use_head(e, batch));
+    const CriticalStreamScope critical(st);  // kernels on `st` outrank the weight-gradient kernels of the side stream
     e->keep_full = false;  // a training step needs only the pooled activations of a fused conv + pool layer
     if (e->comm)
         if (int rc = comm_begin_step(e->comm, st)) return rc;

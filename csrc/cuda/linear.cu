@@ -106,5 +106,5 @@ extern "C" int b200cnn_conv1_pool_bwd_weight(const void* x, int x_is_u8, const f
 }
 extern "C" size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s) {
     // + 128 bytes: completion counter of the single-channel kernel (must be zero before the first use)
-    return size_t(nhwc_bwd_weight_chunks_for(s, nullptr)) * (size_t(s->oc) * s->c * s->k * s->k + s->oc) * sizeof(float) + 128;
+    return nhwc_bwd_weight_scratch_floats(s) * sizeof(float) + 128;
 }

@@ -25,6 +25,21 @@ bool pdl_enabled() {
     return on;
 }
 
+static thread_local cudaStream_t g_critical_stream = nullptr;
+cudaStream_t critical_stream() { return g_critical_stream; }
+int critical_priority() {
+    static const int prio = [] {
+        const char* v = getenv("B200CNN_PRIORITY");
+        if (v && v[0] == '0') return 0;
+        int least = 0, greatest = 0;
+        if (cudaDeviceGetStreamPriorityRange(&least, &greatest) != cudaSuccess) return 0;
+        return greatest;  // numerically lowest = most urgent; 0 when the device has a single level
+    }();
+    return prio;
+}
+CriticalStreamScope::CriticalStreamScope(cudaStream_t st) : saved(g_critical_stream) { g_critical_stream = st; }
+CriticalStreamScope::~CriticalStreamScope() { g_critical_stream = saved; }
+
 }  // namespace b200cnn
 
 extern "C" const char* b200cnn_last_error(void) { return b200cnn::g_error; }

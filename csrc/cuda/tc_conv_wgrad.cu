@@ -20,6 +20,15 @@
 // one-SM funnelling against ~3 us for the second kernel.)
 // Bias gradient: column sums of dz, carried in row 0 of the partial tile (an unused tap row).
 //
+// Stride 1 (kMode 1: the pooled topology's second convolution, 14x14 -> 14x14): the same kernel over other views.
+// Output pixel x reads input pixels x-1, x, x+1, so the pair trick needs the outputs split by the parity of x:
+//   x = 2i:     [kx0 | kx1'] = odd-aligned pair i-1 = pixels (2i-1, 2i),   [kx1 | kx2] = even-aligned pair i
+//   x = 2i + 1: [kx0 | kx1]  = even-aligned pair i,                        [kx1' | kx2] = odd-aligned pair i = (2i+1, 2i+2)
+// (kx1' is a duplicate that the reduction ignores).  "Odd-aligned pairs" are a second tensor map over the same memory
+// shifted by one pixel, with 6 pairs per row: pair -1 and pair 6 are out of bounds = the zero padding.  dz is read
+// through a 5-D map (32 oc, parity, 7, 14, n), so its rows come in the same (y, i) order.  A phase is 2 images
+// (2 x 98 = 196 K rows, again), a CTA owns 4 images of one parity: grid (3 ky, 2 parities, n/4).
+//
 // Replaces the weight half of Layer_feedBack_conv (/root/reference/cnn.c:236,242) for the second convolution.
 #include <cstdlib>
 
@@ -56,12 +65,28 @@ struct WgradArgs {
     long long* dbg;        // instrumentation (B200CNN_WG_DEBUG=1): clock64 stamps of CTAs (ky, z < 4), [ky*4+z][16]
 };
 
+__device__ __forceinline__ void tma_load_5d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3, int c4) {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+}
+
 #define WG_STAMP(i) do { if (a.dbg && blockIdx.z < 4) a.dbg[(ky * 4 + blockIdx.z) * 16 + (i)] = clock64(); } while (0)
 __device__ __forceinline__ void epilogue_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-__global__ void __launch_bounds__(kWgThreads, 1)
-tc_conv3x3s2_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_dz,
-                               WgradArgs a) {
+// kMode 0: stride 2 (tmap_x2 unused); kMode 1: stride 1 (tmap_x = even-aligned pairs, tmap_x2 = odd-aligned pairs).
+// (Registers capped at 85: this kernel shares the SMs with the kernels of the critical path — two of its CTAs at the
+//  146 registers the compiler would take leave no room for a CTA of the first convolution's weight-gradient kernel.)
+template <int kMode>
+__global__ void __launch_bounds__(kWgThreads, 4)
+tc_conv3x3_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_x2,
+                             const __grid_constant__ CUtensorMap tmap_dz, WgradArgs a) {
+    constexpr int kPhaseImgs = kMode ? 2 : b200cnn::kPhaseImgs;  // images per phase (196 K rows either way)
+    constexpr int kIpc = 2 * kPhaseImgs;                         // images per CTA
+    constexpr int kRowsPerImg = kMode ? 196 : kPix;              // dz rows of an image (all parities)
+    constexpr int kBiasRow = kMode ? 16 : 0;                     // a tile row the reduction does not read as a weight
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* a_tile = smem;                        // 2 groups: [unused | kx0], [kx1 | kx2]
@@ -75,11 +100,12 @@ tc_conv3x3s2_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(full_bar + 4);
 
     const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
-    const int ky = blockIdx.x;
+    const int ky = blockIdx.x, parity = blockIdx.y;
     const int n0 = int(blockIdx.z) * kIpc;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_x);
+        if (kMode) prefetch_tmap(&tmap_x2);
         if (!a.dz_chw) prefetch_tmap(&tmap_dz);
         mbar_init(full_bar, 1);
         mbar_init(b_bar, 4);
@@ -106,9 +132,21 @@ tc_conv3x3s2_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const
             for (int h = 0; h < 2; h++) {
                 if (h == 1) { mbar_wait(mma_bar, 0); WG_STAMP(4); }
                 mbar_arrive_expect_tx(full_bar, uint32_t((a.dz_chw ? 2 : 3) * kBoxBytes));
-                tma_load_4d(a_tile, &tmap_x, full_bar, 0, -1, ky - 1, n0 + kPhaseImgs * h);
-                tma_load_4d(a_tile + kTileBytes, &tmap_x, full_bar, 0, 0, ky - 1, n0 + kPhaseImgs * h);
-                if (!a.dz_chw) tma_load_4d(b_tile, &tmap_dz, full_bar, 0, 0, 0, n0 + kPhaseImgs * h);
+                const int img = n0 + kPhaseImgs * h;
+                if (!kMode) {
+                    tma_load_4d(a_tile, &tmap_x, full_bar, 0, -1, ky - 1, img);
+                    tma_load_4d(a_tile + kTileBytes, &tmap_x, full_bar, 0, 0, ky - 1, img);
+                    if (!a.dz_chw) tma_load_4d(b_tile, &tmap_dz, full_bar, 0, 0, 0, img);
+                } else {
+                    if (parity == 0) {
+                        tma_load_4d(a_tile, &tmap_x2, full_bar, 0, -1, ky - 1, img);
+                        tma_load_4d(a_tile + kTileBytes, &tmap_x, full_bar, 0, 0, ky - 1, img);
+                    } else {
+                        tma_load_4d(a_tile, &tmap_x, full_bar, 0, 0, ky - 1, img);
+                        tma_load_4d(a_tile + kTileBytes, &tmap_x2, full_bar, 0, 0, ky - 1, img);
+                    }
+                    tma_load_5d(b_tile, &tmap_dz, full_bar, 0, parity, 0, 0, img);
+                }
             }
         }
     } else if (warp == 1) {
@@ -134,7 +172,7 @@ tc_conv3x3s2_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const
     } else {
         const int w = warp - 2, oc = lane, t = threadIdx.x - 64;
         float s = 0.0f;
-        if (a.dz_chw) {
+        if (kMode == 0 && a.dz_chw) {  // (stride 1 never gets CHW gradients: the branch and its registers compile away)
             // One image at a time: coalesced float4 loads (the next image's already in flight) -> raw[oc][49] ->
             // B[pixel][oc] rows of 128 bytes in the 128B-swizzle-with-32B-atoms layout (32-byte chunk ^= row & 3).
             // Lane = oc on both sides of the transpose: raw reads are 49 floats apart (odd: no bank conflict), tile
@@ -176,11 +214,13 @@ tc_conv3x3s2_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const
 #pragma unroll
                 for (int u = 0; u < 4; u++) cur[u] = nxt[u];
             }
-        } else if (ky == 0) {
+        } else if (ky == 0 && parity == 0) {
             // NHWC: bias gradient straight from global memory (coalesced rows of 32 oc)
-            const float* src = a.dz_nhwc + size_t(n0) * kImgFloats + oc;
+            const float* src = a.dz_nhwc + size_t(n0) * kRowsPerImg * kOC + oc;
+            const int rmax = (a.n - n0) * kRowsPerImg;  // (stride 1: the last CTA may own fewer than kIpc images)
 #pragma unroll 14
-            for (int r = w * (kIpc * kPix / 4); r < (w + 1) * (kIpc * kPix / 4); r++) s += __ldg(src + size_t(r) * kOC);
+            for (int r = w * (kIpc * kRowsPerImg / 4); r < (w + 1) * (kIpc * kRowsPerImg / 4); r++)
+                if (r < rmax) s += __ldg(src + size_t(r) * kOC);
         }
         dbp[w * 32 + oc] = s;
     }
@@ -200,11 +240,11 @@ tc_conv3x3s2_bwd_weight_kernel(const __grid_constant__ CUtensorMap tmap_x, const
 #pragma unroll
         for (int i = 0; i < 16; i++) v[16 + i] = t16[i];
         if (lane < 16) {
-            if (m == 0) {  // row 0 (an unused tap row) carries this CTA's bias-gradient partial
+            if (m == kBiasRow && (kMode == 0 || parity == 0)) {  // a row without a weight in it carries this CTA's bias-gradient partial
 #pragma unroll
                 for (int i = 0; i < 32; i++) v[i] = (dbp[i] + dbp[32 + i]) + (dbp[64 + i] + dbp[96 + i]);
             }
-            float4* out = reinterpret_cast<float4*>(a.part + ((size_t(ky) * gridDim.z + blockIdx.z) * 64 + m) * 32);
+            float4* out = reinterpret_cast<float4*>(a.part + (((size_t(ky) * gridDim.y + parity) * gridDim.z + blockIdx.z) * 64 + m) * 32);
 #pragma unroll
             for (int i = 0; i < 8; i++) out[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         }
@@ -242,6 +282,52 @@ wgrad_reduce_kernel(const float* __restrict__ part, int splits, float* __restric
     for (int i = 0; i < 4; i++) {
         const int oc = oc4 * 4 + i;
         float* dst = is_bias ? db + oc : dw + (size_t(oc) * kC + (row & 15)) * 9 + ky * 3 + (row / 16 - 1);
+        *dst = accumulate ? *dst + sv[i] : sv[i];
+    }
+}
+
+// Stride 1: dW / db from the [3 ky][2 parities][splits] partial tiles.  One WARP per item (4 output channels of one
+// (ky, kx, c), or of the bias): the lanes split the (parity, split) tiles, every load is in flight at once, and a shuffle
+// tree in a fixed order finishes the sum (run-to-run identical).
+__global__ void __launch_bounds__(128)
+wgrad_s1_reduce_kernel(const float* __restrict__ part, int splits, float* __restrict__ dw, float* __restrict__ db, int accumulate) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int item = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
+    constexpr int kItems = 3 * 48 * 8;  // + 8 bias items
+    if (item >= kItems + 8) return;
+    const bool is_bias = item >= kItems;
+    const int tt = is_bias ? item - kItems : item;
+    const int ky = is_bias ? 0 : tt / 384, kx = (tt % 384) / 128, c = (tt % 128) / 8, oc4 = tt % 8;
+    // tile rows: even outputs [kx0 | kx1'] [kx1 | kx2], odd outputs [kx0 | kx1] [kx1' | kx2]; bias: row 16 of parity 0
+    const int row0 = is_bias ? 16 : (kx == 0 ? 0 : kx == 1 ? 32 : 48) + c, row1 = (kx == 0 ? 0 : kx == 1 ? 16 : 48) + c;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int total = (is_bias ? 1 : 2) * splits;
+    for (int j0 = lane; j0 < total; j0 += 4 * 32) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int j = j0 + 32 * u;
+            const int par = j / splits, z = j % splits;
+            v[u] = j < total ? __ldcg(reinterpret_cast<const float4*>(part + (((size_t(ky) * 2 + par) * splits + z) * 64 + (par ? row1 : row0)) * 32) + oc4)
+                             : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s.x += __shfl_xor_sync(0xffffffffu, s.x, o);
+        s.y += __shfl_xor_sync(0xffffffffu, s.y, o);
+        s.z += __shfl_xor_sync(0xffffffffu, s.z, o);
+        s.w += __shfl_xor_sync(0xffffffffu, s.w, o);
+    }
+    if (lane != 0) return;
+    const float sv[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int oc = oc4 * 4 + i;
+        float* dst = is_bias ? db + oc : dw + (size_t(oc) * kC + c) * 9 + ky * 3 + kx;
         *dst = accumulate ? *dst + sv[i] : sv[i];
     }
 }
@@ -294,15 +380,59 @@ int tc_conv3x3s2_bwd_weight(const float* x_nhwc, const float* dz, int dz_is_chw,
     }();
     g_wg_dbg = dbg;
     WgradArgs a{dz_is_chw ? dz : nullptr, dz_is_chw ? nullptr : dz, part, dw, db, s->n, dbg};
-    auto kern = tc_conv3x3s2_bwd_weight_kernel;
+    auto kern = tc_conv3x3_bwd_weight_kernel<0>;
     static bool configured = false;
     if (!configured) {
         B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWgSmem)));
         configured = true;
     }
-    B200CNN_CUDA(launch_kernel(kern, dim3(3, 1, splits), dim3(kWgThreads), kWgSmem, st, tmx, tmdz, a));
+    B200CNN_CUDA(launch_kernel(kern, dim3(3, 1, splits), dim3(kWgThreads), kWgSmem, st, tmx, tmx, tmdz, a));
     B200CNN_CUDA(launch_kernel(wgrad_reduce_kernel, dim3(ceil_div(3 * 48 * 8 + 8, 128)), dim3(128), 0, st, static_cast<const float*>(part), splits, dw, db, accumulate));
     B200CNN_CHECK_LAUNCH("tc_conv3x3s2_bwd_weight");
+    return 0;
+}
+
+bool tc_conv3x3s1_bwd_weight_supported(const b200cnn_conv_shape* s) {
+    return s->k == 3 && s->stride == 1 && s->pad == 1 && s->c == kC && s->oc == kOC && s->oh == 14 && s->ow == 14 && s->h == 14 &&
+           s->w == 14 && s->n >= 1;
+}
+
+size_t tc_conv3x3s1_bwd_weight_scratch_floats(int n) { return size_t(3) * 2 * size_t(ceil_div(n, 4)) * kPartFloats; }
+
+// x: NHWC [n][14][14][16]; dz: NHWC [n][14][14][32]; part: scratch_floats(n) floats.
+int tc_conv3x3s1_bwd_weight(const float* x_nhwc, const float* dz_nhwc, float* dw, float* db, int accumulate, float* part,
+                            const b200cnn_conv_shape* s, cudaStream_t st) {
+    if (!tc_conv3x3s1_bwd_weight_supported(s)) return set_error(kInvalidValue, "tc_conv3x3s1_bwd_weight: unsupported shape");
+    CUtensorMap tme, tmo, tmdz;
+    const uint64_t row = uint64_t(s->w) * kC * 4, img = uint64_t(s->h) * row;
+    {
+        // even-aligned pairs of horizontally adjacent pixels: (32 floats, 7 pairs, H, N) ...
+        const uint64_t dims[4] = {32, 7, uint64_t(s->h), uint64_t(s->n)};
+        const uint64_t strides[4] = {0, 128, row, img};
+        const uint32_t box[4] = {32, 7, 14, 2};
+        if (int rc = encode_tmap_f32(&tme, x_nhwc, 4, dims, strides, box, nullptr, kTmaSw128Atom32)) return rc;
+        // ... and the odd-aligned ones: one pixel further, 6 pairs per row (pair 6 would reach into the next row: it is the padding)
+        const uint64_t dims_o[4] = {32, 6, uint64_t(s->h), uint64_t(s->n)};
+        if (int rc = encode_tmap_f32(&tmo, x_nhwc + kC, 4, dims_o, strides, box, nullptr, kTmaSw128Atom32)) return rc;
+    }
+    {
+        const uint64_t dims[5] = {32, 2, 7, 14, uint64_t(s->n)};
+        const uint64_t strides[5] = {0, 128, 256, 14 * 128, 196 * 128};
+        const uint32_t box[5] = {32, 1, 7, 14, 2};
+        if (int rc = encode_tmap_f32(&tmdz, dz_nhwc, 5, dims, strides, box, nullptr, kTmaSw128Atom32)) return rc;
+    }
+    const int splits = ceil_div(s->n, 4);
+    WgradArgs a{nullptr, dz_nhwc, part, dw, db, s->n, nullptr};
+    auto kern = tc_conv3x3_bwd_weight_kernel<1>;
+    static bool configured = false;
+    if (!configured) {
+        B200CNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWgSmem)));
+        configured = true;
+    }
+    B200CNN_CUDA(launch_kernel(kern, dim3(3, 2, splits), dim3(kWgThreads), kWgSmem, st, tme, tmo, tmdz, a));
+    B200CNN_CUDA(launch_kernel(wgrad_s1_reduce_kernel, dim3(ceil_div((3 * 48 * 8 + 8) * 32, 128)), dim3(128), 0, st, static_cast<const float*>(part),
+                               splits, dw, db, accumulate));
+    B200CNN_CHECK_LAUNCH("tc_conv3x3s1_bwd_weight");
     return 0;
 }
 

@@ -23,6 +23,9 @@ def _cuda_only():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     torch.manual_seed(0)
+    # the PyTorch references are plain fp32 whatever test runs first
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
     yield
     from mpi_cuda_cnn_b200.ops import functional as F200
 
@@ -627,3 +630,40 @@ def test_conv1_pool_fused_forward_and_weight_gradient(n, u8):
         _close(dw.reshape(16, 1, 3, 3), w.grad, 1e-4)
         _close(db, b.grad, 1e-4)
     assert bool((buf[:16] == 7.0).all()) and bool((buf[16 + 144:16 + 144 + 16] == 7.0).all()) and bool((buf[16 + 144 + 32:] == 7.0).all())
+
+
+@pytest.mark.parametrize("n", [1, 3, 4, 66, 256])
+@pytest.mark.parametrize("backend", ["simt", "auto"])
+def test_nhwc_conv2_stride1_weight_gradient(n, backend):
+    """conv2d_bwd_weight_nhwc for the pooled topology's second convolution (16 -> 32 channels at 14x14, stride 1): the
+    tcgen05 split-K implicit GEMM over even / odd pixel pairs (any batch: images past the end are TMA zero fill) and the
+    CUDA-core kernel, twice on one scratch buffer, with and without accumulation, against autograd."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+    from mpi_cuda_cnn_b200.ops import functional as F200
+
+    lib = N.cuda()
+    F200.set_backend(backend)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    torch.backends.cudnn.allow_tf32 = False
+    dz = torch.randn(n, 32, 14, 14, device="cuda")
+    a1 = torch.randn(n, 16, 14, 14, device="cuda")
+    dz_nhwc, a1_nhwc = dz.permute(0, 2, 3, 1).contiguous(), a1.permute(0, 2, 3, 1).contiguous()
+    w = torch.zeros(32, 16, 3, 3, device="cuda", requires_grad=True)
+    F.conv2d(a1, w, None, 1, 1).backward(dz)
+    want_w, want_b = w.grad, dz.sum((0, 2, 3))
+    shp = N.ConvShape(n, 16, 14, 14, 32, 14, 14, 3, 1, 1)
+    scratch = torch.zeros(lib.b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(C.byref(shp)), dtype=torch.uint8, device="cuda")
+    tol = TOL["simt" if backend == "simt" else "tcgen05"]
+    try:
+        for acc in (0, 0, 1):
+            dw = torch.full((32, 16, 3, 3), 7.0, device="cuda")
+            db = torch.full((32,), 7.0, device="cuda")
+            N.check(lib.b200cnn_conv2d_bwd_weight_nhwc(p(a1_nhwc), 0, p(dz_nhwc), 0, p(dw), p(db), acc, p(scratch), C.byref(shp), st), "bwd_weight")
+            torch.cuda.synchronize()
+            _close(dw, want_w + 7.0 * acc, tol)
+            _close(db, want_b + 7.0 * acc, tol)
+    finally:
+        F200.set_backend("auto")
