@@ -114,16 +114,19 @@ def test_emulated_push_protocol_one_gpu(world, two_shot):
         want = views[0][0].double().clone()
 
 
-def _dp_worker(rank, world, mode, algo, steps, out_dir):
+def _dp_worker(rank, world, mode, algo, steps, out_dir, pool=False):
     import os
     import torch
     import torch.distributed as dist
+    from mpi_cuda_cnn_b200 import mnist_layers, pool_layers
     from mpi_cuda_cnn_b200.ops import functional as F200
     from mpi_cuda_cnn_b200.parallel import DataParallelTrainer, init_distributed
 
     rank, world, device = init_distributed()
     B = 64
-    tr = DataParallelTrainer(rank, world, device, batch=B, mode=mode, algo=algo)
+    tr = DataParallelTrainer(rank, world, device, layers=pool_layers() if pool else mnist_layers(), batch=B, mode=mode, algo=algo)
+    if pool:
+        assert tr.engine.conv_path == "tcgen05_pool"
     stream = torch.cuda.Stream()
     with torch.cuda.stream(stream):
         for s in range(steps):
@@ -162,6 +165,32 @@ def test_multi_gpu_fused_equals_single_gpu_big_batch(algo, tmp_path):
     torch.cuda.synchronize()
     ref = eng.get_params()
     # (TF32 products of differently split batches: ~1e-3 per step of drift relative to the largest parameter)
+    assert float(np.abs(reps[0] - ref).max() / np.abs(ref).max()) < 4e-3
+    eng.close()
+
+
+def test_multi_gpu_pooled_topology_fused_equals_single_gpu(tmp_path):
+    """The conv -> pool -> conv -> pool topology on its tensor-core path, data parallel with the fused update: replicas
+    bitwise equal and equal (to TF32 drift) to one GPU training on the concatenated batch."""
+    world = min(torch.cuda.device_count(), 8)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs")
+    from mpi_cuda_cnn_b200 import Engine, pool_layers
+    from mpi_cuda_cnn_b200.ops import functional as F200
+    from mpi_cuda_cnn_b200.parallel import spawn
+
+    steps, B = 4, 64
+    spawn(_dp_worker, world, args=("fused", "auto", steps, str(tmp_path), True))
+    reps = [np.load(tmp_path / f"fused_auto_{r}.npy") for r in range(world)]
+    for r in range(1, world):
+        assert np.array_equal(reps[0], reps[r])
+    eng = Engine(pool_layers(), max_batch=B * world)
+    eng.init_params(seed=0)
+    for s in range(steps):
+        x, y = F200.synthetic_batch(B * world, seed=7, first_index=s * world * B)
+        eng.train_step(x, y, 0.1 / (B * world), use_graph=False)
+    torch.cuda.synchronize()
+    ref = eng.get_params()
     assert float(np.abs(reps[0] - ref).max() / np.abs(ref).max()) < 4e-3
     eng.close()
 
