@@ -99,6 +99,14 @@ int tc_conv1_bwd_weight(const uint8_t* x, const float* dz_nhwc, float* dw, float
                         unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st, float* sgd_w, float* sgd_b,
                         const float* lr_dev, const TailXchg* xchg = nullptr, long w_off = 0, long b_off = 0);
 
+// tc_conv_tail.cu: conv2 backward-data + conv1 weight gradient (+ update / exchange) as one kernel (reference topology)
+bool tc_conv_tail_enabled();
+bool tc_conv_tail_supported(const b200cnn_conv_shape* s2, const b200cnn_conv_shape* s1, int max_partials);
+int tc_conv2dx_conv1dw(const float* dz2, int dz_is_chw, const float* w2, const float* a_prev_nhwc, int act_prev, float* dx_nhwc,
+                       const b200cnn_conv_shape* s2, const uint8_t* x, float* dw1, float* db1, float* partials, unsigned* counter,
+                       const b200cnn_conv_shape* s1, float* sgd_w, float* sgd_b, const float* lr_dev, const TailXchg* xchg, long w_off,
+                       long b_off, int early_w, cudaStream_t st);
+
 // conv_nhwc.cu / conv.cu
 bool nhwc_bwd_weight_supported(const b200cnn_conv_shape* s, int x_is_u8);
 int nhwc_bwd_weight_chunks(int n, int* spb_out);

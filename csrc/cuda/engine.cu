@@ -314,6 +314,14 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             fused_tail = xchg.world() > 1;
         }
     }
+    // Reference topology: the second convolution's data-gradient kernel also produces the first convolution's weight
+    // gradient (tc_conv_tail.cu) — dz1 never leaves the SM and the step loses its last kernel boundary.
+    bool c1_in_dx = false;
+    if (fast && is_u8 && tc_conv_tail_enabled() && L.size() > 3 && L[1].d.type == B200CNN_LAYER_CONV && L[2].d.type == B200CNN_LAYER_CONV &&
+        (!e->comm || fused_tail)) {
+        const b200cnn_conv_shape s1 = conv_shape(L[0], L[1], batch), s2 = conv_shape(L[1], L[2], batch);
+        c1_in_dx = tc_conv_tail_supported(&s2, &s1, nhwc_bwd_weight_chunks(batch, nullptr)) && L[1].act == B200CNN_ACT_RELU;
+    }
     for (size_t li = L.size() - 1; li >= 1; li--) {
         EngineLayer& l = L[li];
         EngineLayer& p = L[li - 1];
@@ -354,7 +362,9 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
             const b200cnn_conv_shape s = conv_shape(p, l, batch);
             const bool nhwc_path = (fast && li <= 2) || (poolc && (li == 1 || li == 3));
             const bool fuse = fuse_update && li == 1;  // single GPU: this kernel's last block also applies the update
-            if (fusedp && li == 1) {
+            if (c1_in_dx && li == 1) {
+                // already produced (and applied / exchanged) by the kernel that computed this layer's dz
+            } else if (fusedp && li == 1) {
                 rc = conv1_pool_bwd_weight(in, in_u8, L[2].dz, L[2].a, L[2].argmax, l.act, grads + l.w_off, grads + l.b_off, 0, e->scratch1,
                                            reinterpret_cast<unsigned*>(e->lr_dev + 8), &s, ws, fuse ? e->params + l.w_off : nullptr,
                                            fuse ? e->params + l.b_off : nullptr, e->lr_dev);
@@ -371,7 +381,7 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
                 rc = launch_conv2d_bwd_weight(l.dz, in, in_u8, grads + l.w_off, grads + l.b_off, 0,
                                               li == 1 ? e->scratch1 : e->scratch, &s, ws);
             // (the single-channel kernel reduces in its last block: one launch; every other path is kernel + reduce)
-            if (launches) (*launches) += (nhwc_path && p.d.depth == 1) ? 1 : 2;
+            if (launches) (*launches) += (c1_in_dx && li == 1) ? 0 : (nhwc_path && p.d.depth == 1) ? 1 : 2;
         }
         if (rc) return rc;
 
@@ -382,7 +392,15 @@ int enqueue_backward(b200cnn_engine* e, const void* images, int is_u8, int batch
                 rc = b200cnn_linear_bwd_data(l.dz, e->params + l.w_off, p.a, p.act, p.dz, batch, l.nnodes, p.nnodes, l.ld, st);
             } else {
                 const b200cnn_conv_shape s = conv_shape(p, l, batch);
-                if (fast && li == 2)
+                if (fast && li == 2 && c1_in_dx) {
+                    const EngineLayer& l1 = L[1];
+                    const b200cnn_conv_shape s1 = conv_shape(L[0], l1, batch);
+                    rc = tc_conv2dx_conv1dw(l.dz, /*dz_is_chw=*/1, e->params + l.w_off, p.a, p.act, /*dx=*/nullptr, &s,
+                                            static_cast<const uint8_t*>(images), grads + l1.w_off, grads + l1.b_off, e->scratch1 + 32,
+                                            reinterpret_cast<unsigned*>(e->lr_dev + 8), &s1, fuse_update ? e->params + l1.w_off : nullptr,
+                                            fuse_update ? e->params + l1.b_off : nullptr, e->lr_dev, fused_tail ? &xchg : nullptr,
+                                            long(l1.w_off), long(l1.b_off), kEarlyW, st);
+                } else if (fast && li == 2)
                     rc = tc_conv3x3s2_bwd_data(l.dz, /*dz_is_chw=*/1, e->params + l.w_off, p.a, p.act, p.dz, &s, st, kEarlyW);
                 else if (poolc && li == 3)  // the layer below is a pool: no activation derivative to apply
                     rc = tc_conv3x3s1_bwd_data(l.dz, e->params + l.w_off, nullptr, B200CNN_ACT_NONE, p.dz, &s, st, kEarlyW);

@@ -180,3 +180,21 @@ def test_host_fed_step_equals_device_step():
     assert counts == [B * (i + 1) for i in range(6)]  # cumulative sample counter, read back after every step
     assert float(loss[5][0]) == pytest.approx(b.read_metrics()["ce_sum"], rel=1e-5)
     a.close(); b.close()
+
+
+def test_fused_backward_tail_kernel_in_child_process():
+    """B200CNN_FUSED_C1=1 (read once per process): the second convolution's data gradient and the first convolution's
+    weight gradient + update as ONE kernel (csrc/cuda/tc_conv_tail.cu).  The engine tests that pin gradients, the update
+    and graph == eager must pass with it on."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, B200CNN_FUSED_C1="1")
+    sel = ["test_forward_backward_step_vs_torch[auto-False]", "test_graph_step_equals_eager_step_and_learns",
+           "test_gpu_engine_tracks_cpu_engine[auto-0.005-False]", "test_host_fed_step_equals_device_step"]
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "-p", "no:cacheprovider"] + [f"{__file__}::{t}" for t in sel],
+                       cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "4 passed" in r.stdout, r.stdout[-2000:]
