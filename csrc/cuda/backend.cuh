@@ -99,6 +99,12 @@ int tc_conv1_bwd_weight(const uint8_t* x, const float* dz_nhwc, float* dw, float
                         unsigned* counter, const b200cnn_conv_shape* s, cudaStream_t st, float* sgd_w, float* sgd_b,
                         const float* lr_dev, const TailXchg* xchg = nullptr, long w_off = 0, long b_off = 0);
 
+// tc_conv12.cu: forward of both convolutions of the reference topology as one kernel (the root of the captured step)
+bool tc_conv12_fwd_enabled();
+bool tc_conv12_fwd_supported(const b200cnn_conv_shape* s1, const b200cnn_conv_shape* s2);
+int tc_conv12_fwd(const uint8_t* x, const float* w1, const float* b1, float* a1_nhwc, int act1, const float* w2, const float* b2, float* y,
+                  int ldy, int act2, const b200cnn_conv_shape* s1, const b200cnn_conv_shape* s2, cudaStream_t st);
+
 // tc_conv_tail.cu: conv2 backward-data + conv1 weight gradient (+ update / exchange) as one kernel (reference topology)
 bool tc_conv_tail_enabled();
 bool tc_conv_tail_supported(const b200cnn_conv_shape* s2, const b200cnn_conv_shape* s1, int max_partials);

@@ -179,6 +179,13 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
     e->nhwc_mask = fast ? 2u : poolc ? 14u : 0u;  // NHWC layers: 1, or 1-3 (the second pool writes CHW rows for the FC layer)
     const bool fusedp = poolc && e->pool_fused;
     e->l1_stale = fusedp && !e->keep_full;
+    // Reference topology: both convolutions in ONE kernel, the root of the captured step (tc_conv12.cu)
+    bool fused12 = false;
+    if (fast && is_u8 && stop > 2 && L.size() > 3 && tc_conv12_fwd_enabled() && L[1].d.type == B200CNN_LAYER_CONV &&
+        L[2].d.type == B200CNN_LAYER_CONV) {
+        const b200cnn_conv_shape s1 = conv_shape(L[0], L[1], batch), s2 = conv_shape(L[1], L[2], batch);
+        fused12 = tc_conv12_fwd_supported(&s1, &s2);
+    }
     for (size_t li = 1; li < L.size() && li < stop; li++) {
         EngineLayer& l = L[li];
         const EngineLayer& p = L[li - 1];
@@ -192,7 +199,15 @@ int enqueue_forward(b200cnn_engine* e, const void* images, int is_u8, const uint
         switch (l.d.type) {
             case B200CNN_LAYER_CONV: {
                 const b200cnn_conv_shape s = conv_shape(p, l, batch);
-                if (fusedp && li == 1)  // convolution + ReLU + the pool above it in one kernel (layer 2 is skipped below)
+                if (fused12 && li == 2) continue;  // computed by the kernel of layer 1
+                if (fused12 && li == 1) {
+                    EngineLayer& l2 = L[2];
+                    const b200cnn_conv_shape s2 = conv_shape(l, l2, batch);
+                    if (e->comm && 2 >= e->wait_layer)  // the kernel reads layer 2's parameters as well
+                        if ((rc = comm_weights_ready(e->comm, st))) return rc;
+                    rc = tc_conv12_fwd(static_cast<const uint8_t*>(in), e->params + l.w_off, e->params + l.b_off, l.a, l.act,
+                                       e->params + l2.w_off, e->params + l2.b_off, l2.a, l2.ld, l2.act, &s, &s2, st);
+                } else if (fusedp && li == 1)  // convolution + ReLU + the pool above it in one kernel (layer 2 is skipped below)
                     rc = conv1_pool_fwd(in, in_u8, e->params + l.w_off, e->params + l.b_off, e->keep_full ? l.a : nullptr, L[2].a,
                                         L[2].argmax, &s, l.act, st);
                 else if ((fast || poolc) && li == 1)  // first conv: CUDA cores (1 input channel), NHWC output for the TMA loads below

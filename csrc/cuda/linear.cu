@@ -92,6 +92,12 @@ extern "C" int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const 
     if (!s || !scratch || !nhwc_bwd_weight_supported(s, x_is_u8)) return set_error(kInvalidValue, "conv2d_bwd_weight_nhwc: unsupported shape or missing scratch");
     return nhwc_conv_bwd_weight(x, x_is_u8, dz, dz_is_chw, dw, db, accumulate, static_cast<float*>(scratch), nullptr, s, as_stream(stream));
 }
+extern "C" int b200cnn_conv12_fwd(const uint8_t* x, const float* w1, const float* b1, float* a1_nhwc, const float* w2, const float* b2,
+                                  float* y, int ldy, const b200cnn_conv_shape* s1, const b200cnn_conv_shape* s2, b200cnn_stream stream) {
+    if (!s1 || !s2 || !x || !w1 || !b1 || !a1_nhwc || !w2 || !b2 || !y) return set_error(kInvalidValue, "conv12_fwd: null argument");
+    if (!tc_conv12_fwd_supported(s1, s2) || ldy < s2->oc * s2->oh * s2->ow) return set_error(kInvalidValue, "conv12_fwd: unsupported shapes");
+    return tc_conv12_fwd(x, w1, b1, a1_nhwc, B200CNN_ACT_RELU, w2, b2, y, ldy, B200CNN_ACT_RELU, s1, s2, as_stream(stream));
+}
 extern "C" int b200cnn_conv1_pool_fwd(const void* x, int x_is_u8, const float* w, const float* b, float* a_full, float* yp,
                                       int32_t* argmax, const b200cnn_conv_shape* s, int act, b200cnn_stream stream) {
     if (!s || !x || !w || !b || !yp || !argmax) return set_error(kInvalidValue, "conv1_pool_fwd: null argument");

@@ -104,6 +104,11 @@ int b200cnn_maxpool_nhwc_bwd(const float* dy, int dy_chw, const int32_t* argmax,
 size_t b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes(const b200cnn_conv_shape* s);
 int b200cnn_conv2d_bwd_weight_nhwc(const void* x, int x_is_u8, const float* dz, int dz_is_chw, float* dw, float* db,
                                    int accumulate, void* scratch, const b200cnn_conv_shape* s, b200cnn_stream stream);
+/* Forward of both convolutions of the reference topology as one kernel (conv 1->16 3x3/s2/p1 + ReLU on the CUDA cores,
+ * written to a1 (NHWC [n][14][14][16]) AND straight into the tcgen05 operand tiles of conv 16->32 3x3/s2/p1 + ReLU).
+ * x: uint8 [n][28][28] (scaled by 1/255); y: [n][ldy], the sample's 32x7x7 outputs CHW-flattened. */
+int b200cnn_conv12_fwd(const uint8_t* x, const float* w1, const float* b1, float* a1_nhwc, const float* w2, const float* b2, float* y,
+                       int ldy, const b200cnn_conv_shape* s1, const b200cnn_conv_shape* s2, b200cnn_stream stream);
 /* First layer of the conv -> pool topology as one kernel: convolution (1 input channel, 3x3, stride 1, pad 1; x uint8
  * scaled by 1/255, or float) + activation + 2x2 / stride-2 max pool.  yp / argmax: NHWC [n][oh/2][ow/2][oc] (argmax = index
  * oy * ow + ox of the winning un-pooled pixel); a_full: NULL, or NHWC [n][oh][ow][oc] to also keep the un-pooled activations.

@@ -135,6 +135,7 @@ def cuda():
     _sig(lib, "b200cnn_maxpool_nhwc_fwd", i, vp, vp, vp, i, i, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_maxpool_nhwc_bwd", i, vp, i, vp, vp, i, vp, i, i, i, i, i, i, vp)
     _sig(lib, "b200cnn_conv2d_bwd_weight_nhwc_scratch_bytes", sz, cs)
+    _sig(lib, "b200cnn_conv12_fwd", i, vp, vp, vp, vp, vp, vp, vp, i, cs, cs, vp)
     _sig(lib, "b200cnn_conv1_pool_fwd", i, vp, i, vp, vp, vp, vp, vp, cs, i, vp)
     _sig(lib, "b200cnn_conv1_pool_bwd_weight", i, vp, i, vp, vp, vp, i, vp, vp, i, vp, cs, vp)
     _sig(lib, "b200cnn_conv2d_bwd_weight_nhwc", i, vp, i, vp, i, vp, vp, i, vp, cs, vp)

@@ -667,3 +667,34 @@ def test_nhwc_conv2_stride1_weight_gradient(n, backend):
             _close(db, want_b + 7.0 * acc, tol)
     finally:
         F200.set_backend("auto")
+
+
+@pytest.mark.parametrize("n", [1, 3, 255, 256])
+def test_conv12_fused_forward_direct(n):
+    """b200cnn_conv12_fwd: both convolutions of the reference topology in one kernel (conv1 on the CUDA cores, written to
+    global memory AND into the tcgen05 operand tiles of conv2) against F.conv2d in fp32; guard columns behind every
+    output row and behind a1 must stay untouched."""
+    import ctypes as C
+
+    from mpi_cuda_cnn_b200 import _native as N
+
+    lib = N.cuda()
+    x = torch.randint(0, 256, (n, 1, 28, 28), device="cuda", dtype=torch.uint8)
+    w1, b1 = 0.3 * torch.randn(16, 1, 3, 3, device="cuda"), 0.1 * torch.randn(16, device="cuda")
+    w2, b2 = 0.2 * torch.randn(32, 16, 3, 3, device="cuda"), 0.1 * torch.randn(32, device="cuda")
+    a1_ref = torch.relu(F.conv2d(x.float() / 255.0, w1, b1, 2, 1))
+    a2_ref = torch.relu(F.conv2d(a1_ref, w2, b2, 2, 1))
+    s1 = N.ConvShape(n, 1, 28, 28, 16, 14, 14, 3, 1, 2)
+    s2 = N.ConvShape(n, 16, 14, 14, 32, 7, 7, 3, 1, 2)
+    ldy = 32 * 49 + 16
+    p = lambda t: C.c_void_p(t.data_ptr())
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for rep in range(2):
+        a1 = torch.full((n * 14 * 14 * 16 + 64,), 7.0, device="cuda")
+        y = torch.full((n, ldy), 7.0, device="cuda")
+        N.check(lib.b200cnn_conv12_fwd(p(x), p(w1), p(b1), p(a1), p(w2), p(b2), p(y), ldy, C.byref(s1), C.byref(s2), st), "conv12_fwd")
+        torch.cuda.synchronize()
+        _close(a1[:n * 3136].reshape(n, 14, 14, 16).permute(0, 3, 1, 2), a1_ref, 1e-5)
+        assert bool((a1[n * 3136:] == 7.0).all())
+        _close(y[:, :1568].reshape(n, 32, 7, 7), a2_ref, 4e-3)
+        assert bool((y[:, 1568:] == 7.0).all())
