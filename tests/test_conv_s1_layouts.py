@@ -1,10 +1,11 @@
-"""Index algebra of the stride-1 tensor-core convolution kernels, replayed in numpy on CPU (the kernels themselves are
+"""Index algebra of the tensor-core convolution kernels added in round 2, replayed in numpy on CPU (the kernels themselves are
 tested on hardware in tests/test_gpu_ops.py; this pins the formulations they implement, element for element):
 
 * csrc/cuda/tc_conv_halo.cu: ONE load of a band with a one-pixel halo, padded to width 16; tap (ky, kx) is the same tile
   read from row (ky * 16 + kx) on — forward and, with mirrored taps, backward-data;
 * csrc/cuda/tc_conv_wgrad.cu, kMode 1: the weight gradient over even- / odd-aligned pixel pairs with the outputs split by
-  the parity of x, including the out-of-bounds pairs that stand for the zero padding and the tile rows the reduction reads.
+  the parity of x, including the out-of-bounds pairs that stand for the zero padding and the tile rows the reduction reads;
+* csrc/cuda/tc_conv12.cu: the first convolution's pixels scattered into the tap tiles of the second (stride-2) convolution.
 """
 import numpy as np
 import torch
@@ -102,3 +103,40 @@ def test_even_odd_pair_weight_gradient_matches_autograd():
             for kx in range(3):
                 got[:, :, ky, kx] += tile[row_of[kx]:row_of[kx] + 16].T
     assert np.abs(got - want).max() < 1e-9
+
+
+def test_conv12_scatter_into_tap_tiles_matches_conv2d():
+    """csrc/cuda/tc_conv12.cu: every pixel (y, x) of the first convolution's output is written into row (j, i) of the tap
+    tile (ky, kx) wherever y = 2j - 1 + ky and x = 2i - 1 + kx (1, 2 or 4 tiles); rows whose source lies in the zero
+    padding are cleared beforehand.  The nine tile GEMMs must add up to the stride-2 convolution."""
+    rng = np.random.default_rng(3)
+    a1 = rng.standard_normal((16, 14, 14))
+    w2 = rng.standard_normal((32, 16, 3, 3))
+    want = F.conv2d(torch.from_numpy(a1)[None], torch.from_numpy(w2), None, 2, 1)[0].numpy()
+    tiles = np.full((9, 49, 16), np.nan)  # NaN = never written
+    for tap in range(9):
+        for row in range(49):
+            j, i = row // 7, row % 7
+            if 2 * j - 1 + tap // 3 < 0 or 2 * i - 1 + tap % 3 < 0:
+                tiles[tap, row] = 0.0
+    writes = np.zeros((14, 14), dtype=int)
+    for y in range(14):
+        for x in range(14):
+            for ky in range(3):
+                jy = y + 1 - ky
+                if jy % 2 or jy < 0 or jy >= 14:
+                    continue
+                for kx in range(3):
+                    ix = x + 1 - kx
+                    if ix % 2 or ix < 0 or ix >= 14:
+                        continue
+                    row = (jy // 2) * 7 + ix // 2
+                    assert np.isnan(tiles[ky * 3 + kx, row]).all(), "a tile row is written once"
+                    tiles[ky * 3 + kx, row] = a1[:, y, x]
+                    writes[y, x] += 1
+    assert not np.isnan(tiles).any(), "every row of every tap tile is either padding or some pixel"
+    assert set(np.unique(writes)) <= {1, 2, 4}
+    got = np.zeros((49, 32))
+    for tap in range(9):
+        got += tiles[tap] @ w2[:, :, tap // 3, tap % 3].T
+    assert np.abs(got.T.reshape(32, 7, 7) - want).max() < 1e-10
