@@ -13,6 +13,8 @@
 //                  --pool --backend auto|simt|tcgen05 --save F --load F --timing
 //                  --algo auto|one_shot|two_shot|ll_one_shot|ll_two_shot] train-images train-labels test-images test-labels
 #include <cuda_runtime.h>
+
+#include <algorithm>
 #include <sys/mman.h>
 #include <sys/wait.h>
 #include <unistd.h>
@@ -62,6 +64,23 @@ int run_rank(int rank, int world, const app::Options& o, Shared* sh, ShmComm& ho
         FAIL(1);
     }
     CU(cudaSetDevice(rank));
+    if (rank == 0 && world > 1) {
+        // NVLink topology as the CUDA runtime sees it from GPU 0 (informational, like the Python launcher's line): peers
+        // reachable by load/store, peers with native atomics over the link, best / worst P2P performance rank.
+        int reach = 0, atomics = 0, best = 1 << 30, worst = -1;
+        for (int d = 1; d < world; d++) {
+            int ok = 0, at = 0, perf = 0;
+            if (cudaDeviceCanAccessPeer(&ok, 0, d) == cudaSuccess && ok) reach++;
+            if (cudaDeviceGetP2PAttribute(&at, cudaDevP2PAttrNativeAtomicSupported, 0, d) == cudaSuccess && at) atomics++;
+            if (cudaDeviceGetP2PAttribute(&perf, cudaDevP2PAttrPerformanceRank, 0, d) == cudaSuccess) {
+                best = std::min(best, perf);
+                worst = std::max(worst, perf);
+            }
+        }
+        cudaGetLastError();  // (an unsupported attribute query must not poison later error checks)
+        fprintf(stderr, "topology: %d GPUs, peers reachable from GPU 0: %d/%d, native atomics: %d/%d, P2P performance rank %d..%d\n", world, reach,
+                world - 1, atomics, world - 1, worst < 0 ? 0 : best, worst < 0 ? 0 : worst);
+    }
     CK(b200cnn_set_backend(o.backend));
     const std::vector<b200cnn_layer_desc> layers = app::topology(o.pool);
     b200cnn_engine* eng = b200cnn_engine_create(layers.data(), int(layers.size()), o.batch);
