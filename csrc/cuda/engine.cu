@@ -11,6 +11,16 @@
 // kernel).  Data parallel: the buffers live in the communicator's NVLink-mapped region and the fused
 // all-reduce + SGD runs per BUCKET of adjacent layer slices (>= 512 KiB, or whatever is left at the first
 // layer), each launched as soon as its last gradient exists.
+//
+// Topologies with their own kernel chains (detected in b200cnn_engine_create, reported by b200cnn_engine_conv_path):
+//   conv(1->16, s2) -> conv(16->32, s2) -> FC...     both forward convolutions in ONE root kernel (tc_conv12.cu), tcgen05
+//                                                    implicit GEMMs for conv2 forward / backward-data / weight gradient,
+//                                                    tcgen05 weight gradient for conv1 with the update (or the exchange
+//                                                    with the peers) in its last block;
+//   conv -> pool -> conv -> pool -> FC...            fused conv1 + pool, one-load halo convolutions (tc_conv_halo.cu),
+//                                                    stride-1 tcgen05 weight gradient, conv1's weight gradient from the
+//                                                    pooled gradient;
+//   anything else                                    the generic CHW kernels of conv.cu / pool.cu and the tcgen05 / SIMT GEMMs.
 #include <cstdlib>
 #include <cstring>
 #include <vector>
