@@ -506,15 +506,19 @@ def test_tcgen05_conv3x3_stride1_banded_nhwc_out(n, act):
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     code = N.ACT_RELU if act == "relu" else N.ACT_NONE
     xn = x.permute(0, 2, 3, 1).contiguous()
-    y = torch.full((n, 14, 14, 32), 7.0, device="cuda")
+    # (the one-load kernel computes 16 columns per image row and two rows past the image: none of that may be stored)
+    ybuf = torch.full((n * 14 * 14 * 32 + 512,), 7.0, device="cuda")
+    y = ybuf[:n * 14 * 14 * 32].view(n, 14, 14, 32)
     N.check(lib.b200cnn_conv3x3_fwd_nhwc_to_nhwc(p(xn), p(w), p(b), p(y), C.byref(shp), code, st), "conv3x3_fwd_nhwc_to_nhwc")
     torch.cuda.synchronize()
     _close(y.permute(0, 3, 1, 2), want, 4e-3)
-    ldy = 32 * 196
+    assert bool((ybuf[n * 14 * 14 * 32:] == 7.0).all())
+    ldy = 32 * 196 + 16
     y2 = torch.full((n, ldy), 7.0, device="cuda")
     N.check(lib.b200cnn_conv3x3_fwd_nhwc(p(xn), p(w), p(b), p(y2), ldy, C.byref(shp), code, st), "conv3x3_fwd_nhwc")
     torch.cuda.synchronize()
-    _close(y2.reshape(n, 32, 14, 14), want, 4e-3)
+    _close(y2[:, :32 * 196].reshape(n, 32, 14, 14), want, 4e-3)
+    assert bool((y2[:, 32 * 196:] == 7.0).all())
 
 
 @pytest.mark.parametrize("n", [1, 3, 64])
@@ -533,7 +537,8 @@ def test_tcgen05_conv3x3_stride1_backward_data(n, mask):
     want = F.conv_transpose2d(dz, w, None, 1, 1)
     if mask:
         want = want * (a_prev > 0)
-    dx = torch.full((n, 14, 14, 16), 7.0, device="cuda")
+    dxbuf = torch.full((n * 14 * 14 * 16 + 512,), 7.0, device="cuda")
+    dx = dxbuf[:n * 14 * 14 * 16].view(n, 14, 14, 16)
     shp = N.ConvShape(n, 16, 14, 14, 32, 14, 14, 3, 1, 1)
     p = lambda t: C.c_void_p(t.data_ptr())
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -542,6 +547,7 @@ def test_tcgen05_conv3x3_stride1_backward_data(n, mask):
                                                 N.ACT_RELU if mask else N.ACT_NONE, p(dx), C.byref(shp), st), "conv3x3s1_bwd_data_nhwc")
     torch.cuda.synchronize()
     _close(dx.permute(0, 3, 1, 2), want, 4e-3)
+    assert bool((dxbuf[n * 14 * 14 * 16:] == 7.0).all())  # nothing stored for the padded columns / rows past the image
 
 
 @pytest.mark.parametrize("shape", [(5, 16, 28, 28), (3, 32, 14, 14)])
