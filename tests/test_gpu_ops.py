@@ -665,12 +665,13 @@ def test_nhwc_conv2_stride1_weight_gradient(n, backend):
     tol = TOL["simt" if backend == "simt" else "tcgen05"]
     try:
         for acc in (0, 0, 1):
-            dw = torch.full((32, 16, 3, 3), 7.0, device="cuda")
-            db = torch.full((32,), 7.0, device="cuda")
+            buf = torch.full((64 + 4608 + 64 + 32 + 64,), 7.0, device="cuda")  # canaries in front of, between and behind dw / db
+            dw, db = buf[64:64 + 4608].view(32, 16, 3, 3), buf[64 + 4608 + 64:64 + 4608 + 64 + 32]
             N.check(lib.b200cnn_conv2d_bwd_weight_nhwc(p(a1_nhwc), 0, p(dz_nhwc), 0, p(dw), p(db), acc, p(scratch), C.byref(shp), st), "bwd_weight")
             torch.cuda.synchronize()
             _close(dw, want_w + 7.0 * acc, tol)
             _close(db, want_b + 7.0 * acc, tol)
+            assert bool((buf[:64] == 7.0).all()) and bool((buf[64 + 4608:64 + 4608 + 64] == 7.0).all()) and bool((buf[-64:] == 7.0).all())
     finally:
         F200.set_backend("auto")
 
